@@ -1,0 +1,218 @@
+/*
+ * rt_b200.h — C ABI of the B200-native ray-tracing core (librt_b200.so).
+ *
+ * This is the drop-in boundary for the render path of mcan1999/vulkan-raytracing.
+ * The reference has no plugin/FFI interface: the path is inlined in main()
+ * (src/main.cpp).  Each entry point below names the reference code it replaces.
+ * Citations are relative to /root/reference.
+ *
+ * Conventions:
+ *   - plain pointers and sizes only; no C++/torch types cross the boundary;
+ *   - caller keeps ownership of every input; the library copies what it needs to
+ *     HBM at rt_scene_build time (reference: main.cpp:291-294, 2110-2113);
+ *   - every call returns RT_OK (0) or a negative rt_status; nothing throws across
+ *     the boundary (the reference throws std::runtime_error, main.cpp:138-147);
+ *     rt_last_error() returns a thread-local message for the last failure;
+ *   - calls are synchronous on return unless stated; a scene handle is not
+ *     re-entrant; there is NO CPU fallback: without a CUDA device every compute
+ *     entry point fails with RT_ERR_NO_DEVICE.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_B200_ABI_VERSION 1u
+
+typedef enum rt_status {
+  RT_OK = 0,
+  RT_ERR_INVALID_ARGUMENT = -1,
+  RT_ERR_NO_DEVICE = -2,
+  RT_ERR_CUDA = -3,
+  RT_ERR_OUT_OF_MEMORY = -4,
+  RT_ERR_UNSUPPORTED = -5
+} rt_status;
+
+/* Object (material) types — include/config.h:9-16, shader.rgen:35-41. */
+enum { RT_TYPE_DIFFUSE = 0, RT_TYPE_MIRROR = 1, RT_TYPE_REFRACTIVE = 2 };
+
+/* Output pixel formats.  RGBA8 = rint(clamp(c,0,1)*255), no sRGB encode: the
+ * reference stores into an 8-bit UNORM surface-format image (main.cpp:1899).
+ * RGBA32F is the value the shader hands to imageStore (shader.rgen:183-185). */
+enum { RT_FORMAT_RGBA8 = 0, RT_FORMAT_RGBA32F = 1 };
+enum { RT_LOCATION_HOST = 0, RT_LOCATION_DEVICE = 1 };
+
+/* Acceleration-structure flavours (rt_scene_desc.flags, low 4 bits). */
+enum {
+  RT_ACCEL_DEFAULT = 0,   /* compressed 8-wide BVH (the product path)           */
+  RT_ACCEL_BVH2 = 1,      /* plain Karras LBVH, binary traversal (cross-check)   */
+  RT_ACCEL_BRUTE = 2      /* no hierarchy: every ray tests every triangle (tiny
+                             scenes only; parity cross-check)                    */
+};
+#define RT_FLAG_ACCEL_MASK 0xFu
+
+/* One triangle mesh = one bottom-level acceleration structure.
+ * Replaces createBLASGeometry/createBLAS/buildBLAS (main.cpp:305-536) and the
+ * vertex/index packing they read (main.cpp:1660-1729):
+ *   vertices: n_vertices x [px,py,pz,nx,ny,nz] FP32, stride 24 B (main.cpp:1678-1683)
+ *   indices : n_triangles x 3 uint32, mesh-local vertex_index (main.cpp:1647-1649) */
+typedef struct rt_mesh_desc {
+  const float* vertices;
+  uint32_t n_vertices;
+  const uint32_t* indices;
+  uint32_t n_triangles;
+} rt_mesh_desc;
+
+/* One instance of a mesh.  Replaces createInstance (main.cpp:538-551):
+ *   transform = row-major 3x4 object-to-world, i.e. VkTransformMatrixKHR
+ *   (glmToVulkan, main.cpp:245-249); instanceCustomIndex = the instance's index
+ *   in the array; mask 0xFF; triangle facing cull disabled; geometry opaque.
+ *   type = CENTER_MESH_TYPE / ORBITING_MESH_TYPE of config.h:15-16. */
+typedef struct rt_instance_desc {
+  uint32_t mesh;
+  uint32_t type;
+  float transform[12];
+} rt_instance_desc;
+
+/* Replaces main.cpp:1603-1835 (meshes, BLAS, instances, TLAS) and 2061-2412
+ * (skybox cube image + sampler).
+ *   skybox_rgba8: 6 faces, layer order +X,-X,+Y,-Y,+Z,-Z = right,left,top,bottom,
+ *   front,back (main.cpp:2064-2071), each sky_w x sky_h RGBA8 rows top-down,
+ *   R8G8B8A8_UNORM (main.cpp:2124), sampled bilinear clamp-to-edge
+ *   (main.cpp:2393-2399).  May be NULL: misses then return black. */
+typedef struct rt_scene_desc {
+  uint32_t n_meshes;
+  const rt_mesh_desc* meshes;
+  uint32_t n_instances;
+  const rt_instance_desc* instances;
+  const uint8_t* skybox_rgba8;
+  uint32_t sky_w, sky_h;
+  int32_t device_id;      /* CUDA ordinal; -1 = current device */
+  uint32_t flags;         /* RT_ACCEL_* */
+} rt_scene_desc;
+
+/* Camera vectors exactly as they reach the uniform block (main.cpp:1848-1851,
+ * 2879-2898): Camera::getPosition/RightVector/UpVector/FrontVector. */
+typedef struct rt_camera {
+  float position[3];
+  float right[3];
+  float up[3];
+  float forward[3];
+} rt_camera;
+
+/* Per-frame parameters = the rest of UniformStructure (main.cpp:1853-1857) plus
+ * the launch size of vkCmdTraceRaysKHR (main.cpp:2620-2624) and the output
+ * description.  Sharding (multi-GPU): the frame is cut into tiles of
+ * tile_w x tile_h pixels, numbered row-major; shard s of n renders the tiles
+ * with (tile_index % n) == s, using GLOBAL pixel coordinates and the GLOBAL
+ * launch size for ray generation, and writes them compactly, tile after tile
+ * (each tile_w*tile_h pixels row-major, edge tiles padded) in increasing
+ * tile_index order.  shard_count <= 1 renders the full frame, row-major. */
+typedef struct rt_frame_params {
+  uint32_t width, height;
+  uint32_t max_bounce_count;      /* MAX_BOUNCE_COUNT, config.h:26 */
+  uint32_t samples_per_pixel;     /* SAMPLES_PER_PIXEL, config.h:27 */
+  float light_position[3];        /* {5,5,5}, main.cpp:1853 */
+  float light_intensity;          /* 1.0, main.cpp:1854 */
+  uint32_t output_format;         /* RT_FORMAT_* */
+  uint32_t output_location;       /* RT_LOCATION_* */
+  uint32_t shard_index, shard_count;
+  uint32_t tile_w, tile_h;        /* 0 = default 64x64 */
+} rt_frame_params;
+
+/* Hit record of one closest-hit trace (what the driver hands shader.rchit:
+ * gl_InstanceCustomIndexEXT, gl_PrimitiveID, hitCoordinate, gl_HitTEXT). */
+typedef struct rt_hit {
+  uint32_t instance;   /* 0xFFFFFFFF = miss */
+  uint32_t primitive;
+  float t, u, v;
+} rt_hit;
+
+/* Counters of the last rt_render_frame / rt_scene_build on this scene.
+ * rays_* count traceRayEXT-equivalents actually issued. nodes/tris are filled
+ * only when the frame was rendered with rt_set_counting(scene, 1). */
+typedef struct rt_stats {
+  double build_ms;            /* all BLAS builds + TLAS, CUDA events */
+  double frame_ms;            /* last frame, CUDA events, device side only */
+  double trace_ms;            /* closest-hit traversal kernels of the last frame */
+  double shadow_ms;           /* shadow traversal kernels */
+  double shade_ms;            /* raygen + shading + resolve kernels */
+  uint64_t rays_primary;      /* closest-hit traces at bounce 0 */
+  uint64_t rays_secondary;    /* closest-hit traces at bounce >= 1 */
+  uint64_t rays_shadow;
+  uint64_t n_miss;            /* skybox lookups */
+  uint64_t n_hit;             /* closest-hit shading events */
+  uint64_t nodes_visited;     /* wide (or binary) nodes popped and tested */
+  uint64_t tris_tested;       /* ray-triangle tests executed */
+  uint64_t kernel_launches;   /* kernels launched by the last frame */
+  uint64_t bvh_nodes;         /* node count over all BLAS */
+  uint64_t bvh_bytes;         /* HBM bytes of nodes + leaf triangles */
+  uint32_t node_bytes;        /* bytes per node of the active layout */
+  uint32_t tri_bytes;         /* bytes per leaf triangle of the active layout */
+  uint32_t ray_state_bytes;   /* bytes of ray state written then read per ray */
+  uint32_t reserved;
+} rt_stats;
+
+/* --- library ---------------------------------------------------------------- */
+uint32_t rt_abi_version(void);
+const char* rt_last_error(void);
+/* Number of CUDA devices visible; 0 when there is none (never an error). */
+int rt_device_count(void);
+
+/* --- scene ------------------------------------------------------------------ */
+/* main.cpp:1603-1835 + 2061-2412.  Builds every BLAS on the GPU. */
+int rt_scene_build(const rt_scene_desc* desc, void** out_scene);
+/* Per-frame instance transforms: the TLAS UPDATE of main.cpp:2836-2861, without
+ * the blocking rebuild.  xforms12 = n_instances x 12 floats, row-major 3x4. */
+int rt_scene_set_transforms(void* scene, const float* xforms12, uint32_t n_instances);
+/* main.cpp:2974-3062. */
+int rt_scene_destroy(void* scene);
+/* CUDA stream (cudaStream_t) all later work of this scene is issued on;
+ * NULL = the legacy default stream (the default). */
+int rt_scene_set_stream(void* scene, void* cuda_stream);
+/* 1 = count nodes_visited / tris_tested in the traversal kernels (slower). */
+int rt_set_counting(void* scene, int enable);
+
+/* --- frame ------------------------------------------------------------------ */
+/* vkCmdTraceRaysKHR(width,height,1) (main.cpp:2620-2624) running shader.rgen /
+ * shader.rchit / shader.rmiss / shader_shadow.rmiss, then the image store.
+ * rgba_out: host or device pointer per params->output_location, sized
+ * rt_frame_output_bytes(params). */
+int rt_render_frame(void* scene, const rt_camera* camera, const rt_frame_params* params,
+                    void* rgba_out);
+uint64_t rt_frame_output_bytes(const rt_frame_params* params);
+/* Number of pixels shard `shard_index` writes (padded tiles included). */
+uint64_t rt_frame_shard_pixels(const rt_frame_params* params);
+/* De-interleave gathered shard buffers into a row-major frame, on the device.
+ * gathered = shard 0's buffer, then shard 1's, ... each rt_frame_shard_pixels
+ * long (device pointer); frame_out = width*height pixels (device pointer). */
+int rt_assemble_shards(void* scene, const rt_frame_params* params, const void* gathered,
+                       void* frame_out);
+
+/* --- parity / measurement exports --------------------------------------------- */
+/* Primary-ray hit records of a frame: width*height*samples_per_pixel records,
+ * index = (y*width + x)*spp + sample.  hits_out is a HOST pointer. */
+int rt_primary_hits(void* scene, const rt_camera* camera, const rt_frame_params* params,
+                    rt_hit* hits_out);
+/* Closest-hit (any_hit = 0) or any-hit (any_hit = 1) traces of an arbitrary ray
+ * batch: traceRayEXT of shader.rgen:86 / :111.  origins/dirs: n x 3 floats
+ * (HOST); tmin/tmax scalars.  For any_hit only hits_out[i].instance (0 or
+ * 0xFFFFFFFF) is meaningful. */
+int rt_trace_rays(void* scene, uint64_t n, const float* origins, const float* dirs,
+                  float tmin, float tmax, int any_hit, rt_hit* hits_out);
+int rt_get_stats(void* scene, rt_stats* out);
+
+/* --- sorting primitive (exported for tests) ---------------------------------- */
+/* The radix sort the LBVH build uses: sorts n (key,value) pairs by key, stable.
+ * HOST pointers; keys_out/vals_out may alias the inputs. */
+int rt_debug_sort_pairs(int device_id, uint64_t n, const uint64_t* keys_in,
+                        const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

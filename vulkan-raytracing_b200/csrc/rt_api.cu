@@ -1,0 +1,404 @@
+// rt_api.cu — the C ABI of librt_b200.so (include/rt_b200.h).  Host-side glue only:
+// argument checking, device memory ownership, instance matrices; all ray tracing happens
+// in the kernels of rt_build.cu / rt_render.cu.  No CPU fallback exists: every compute
+// entry point fails with RT_ERR_NO_DEVICE when no CUDA device is usable.
+#include <cmath>
+#include <cstring>
+#include <memory>
+
+#include "rt_internal.h"
+
+namespace rt {
+
+thread_local std::string g_err;
+
+struct Scene {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  uint32_t accel = ACCEL_WIDE;
+  std::vector<BlasHost> blas;
+  std::vector<InstDev> inst;
+  BlasDev* d_blas = nullptr;
+  InstDev* d_inst = nullptr;
+  uint8_t* d_sky = nullptr;
+  uint32_t sky_w = 0, sky_h = 0;
+  FramePipeline* pipe = nullptr;
+  void* d_out = nullptr;
+  size_t d_out_bytes = 0;
+  bool counting = false;
+  rt_stats stats{};
+
+  SceneDev dev() const {
+    SceneDev s{};
+    s.blas = d_blas;
+    s.inst = d_inst;
+    s.n_inst = (uint32_t)inst.size();
+    s.accel = accel;
+    s.sky = d_sky;
+    s.sky_w = sky_w;
+    s.sky_h = sky_h;
+    return s;
+  }
+};
+
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+
+// inverse of a row-major 3x4 affine matrix: adjugate / determinant in double, rounded to
+// float (numeric contract; the oracle uses the same formula independently)
+static void invert34(const float* m, float* out) {
+  const double a = m[0], b = m[1], c = m[2], d = m[4], e = m[5], f = m[6], g = m[8], h = m[9], i = m[10];
+  const double tx = m[3], ty = m[7], tz = m[11];
+  const double A = e * i - f * h, B = c * h - b * i, C = b * f - c * e;
+  const double D = f * g - d * i, E = a * i - c * g, F = c * d - a * f;
+  const double G = d * h - e * g, H = b * g - a * h, I = a * e - b * d;
+  const double det = a * A + b * D + c * G;
+  const double r = 1.0 / det;
+  const double n[9] = {A * r, B * r, C * r, D * r, E * r, F * r, G * r, H * r, I * r};
+  out[0] = (float)n[0]; out[1] = (float)n[1]; out[2] = (float)n[2];
+  out[4] = (float)n[3]; out[5] = (float)n[4]; out[6] = (float)n[5];
+  out[8] = (float)n[6]; out[9] = (float)n[7]; out[10] = (float)n[8];
+  out[3] = (float)(-(n[0] * tx + n[1] * ty + n[2] * tz));
+  out[7] = (float)(-(n[3] * tx + n[4] * ty + n[5] * tz));
+  out[11] = (float)(-(n[6] * tx + n[7] * ty + n[8] * tz));
+}
+
+static void set_instance(Scene& s, uint32_t i, const float* xf) {
+  InstDev& in = s.inst[i];
+  memcpy(in.o2w, xf, sizeof(float) * 12);
+  invert34(xf, in.w2o);
+  const BlasHost& b = s.blas[in.mesh];
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  for (int c = 0; c < 8; c++) {
+    const double p[3] = {(c & 1) ? b.hi[0] : b.lo[0], (c & 2) ? b.hi[1] : b.lo[1], (c & 4) ? b.hi[2] : b.lo[2]};
+    for (int r = 0; r < 3; r++) {
+      const double w = (double)xf[4 * r] * p[0] + (double)xf[4 * r + 1] * p[1] + (double)xf[4 * r + 2] * p[2] + (double)xf[4 * r + 3];
+      lo[r] = std::min(lo[r], w);
+      hi[r] = std::max(hi[r], w);
+    }
+  }
+  for (int r = 0; r < 3; r++) {
+    const double pad = 1e-5 * std::max(std::fabs(lo[r]), std::fabs(hi[r])) + 1e-5 * (hi[r] - lo[r]) + 1e-30;
+    in.wlo[r] = (float)(lo[r] - pad);
+    in.whi[r] = (float)(hi[r] + pad);
+  }
+}
+
+static int upload_instances(Scene& s) {
+  if (s.inst.empty()) return RT_OK;
+  RT_CUDA_TRY(cudaMemcpyAsync(s.d_inst, s.inst.data(), s.inst.size() * sizeof(InstDev), cudaMemcpyHostToDevice, s.stream), g_err);
+  RT_CUDA_TRY(cudaStreamSynchronize(s.stream), g_err);
+  return RT_OK;
+}
+
+static void destroy_scene(Scene* s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  for (auto& b : s->blas) free_blas(b);
+  cudaFree(s->d_blas); cudaFree(s->d_inst); cudaFree(s->d_sky); cudaFree(s->d_out);
+  pipeline_destroy(s->pipe);
+  delete s;
+}
+
+static int fill_uniforms(const rt_camera* cam, const rt_frame_params* p, FrameUniforms& U) {
+  if (!cam || !p) return fail(RT_ERR_INVALID_ARGUMENT, "null camera or params");
+  if (p->width == 0 || p->height == 0 || p->samples_per_pixel == 0) return fail(RT_ERR_INVALID_ARGUMENT, "empty frame");
+  if (p->output_format > RT_FORMAT_RGBA32F || p->output_location > RT_LOCATION_DEVICE)
+    return fail(RT_ERR_INVALID_ARGUMENT, "bad output format/location");
+  U.position = mk3(cam->position[0], cam->position[1], cam->position[2]);
+  U.right = mk3(cam->right[0], cam->right[1], cam->right[2]);
+  U.up = mk3(cam->up[0], cam->up[1], cam->up[2]);
+  U.forward = mk3(cam->forward[0], cam->forward[1], cam->forward[2]);
+  U.light = mk3(p->light_position[0], p->light_position[1], p->light_position[2]);
+  U.intensity = p->light_intensity;
+  U.width = p->width; U.height = p->height;
+  U.max_bounce = p->max_bounce_count; U.spp = p->samples_per_pixel;
+  U.tile_w = p->tile_w ? p->tile_w : 64; U.tile_h = p->tile_h ? p->tile_h : 64;
+  if (U.tile_w % 8 || U.tile_h % 4) return fail(RT_ERR_INVALID_ARGUMENT, "tile_w must be a multiple of 8, tile_h of 4");
+  U.tiles_x = (U.width + U.tile_w - 1) / U.tile_w;
+  U.tiles_y = (U.height + U.tile_h - 1) / U.tile_h;
+  U.shard_count = p->shard_count ? p->shard_count : 1;
+  U.shard_index = p->shard_index;
+  if (U.shard_index >= U.shard_count) return fail(RT_ERR_INVALID_ARGUMENT, "shard_index >= shard_count");
+  const uint32_t tiles = U.tiles_x * U.tiles_y;
+  U.n_local_tiles = tiles > U.shard_index ? (tiles - U.shard_index + U.shard_count - 1) / U.shard_count : 0;
+  return RT_OK;
+}
+
+static uint64_t shard_pixels(const rt_frame_params* p) {
+  const uint32_t tw = p->tile_w ? p->tile_w : 64, th = p->tile_h ? p->tile_h : 64;
+  const uint64_t tiles = (uint64_t)((p->width + tw - 1) / tw) * ((p->height + th - 1) / th);
+  const uint32_t n = p->shard_count ? p->shard_count : 1;
+  return ((tiles + n - 1) / n) * tw * th;
+}
+
+}  // namespace rt
+
+using namespace rt;
+
+extern "C" {
+
+uint32_t rt_abi_version(void) { return RT_B200_ABI_VERSION; }
+const char* rt_last_error(void) { return g_err.c_str(); }
+
+int rt_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
+  if (!d || !out_scene) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  *out_scene = nullptr;
+  if (d->n_meshes == 0 || !d->meshes || (d->n_instances && !d->instances)) return fail(RT_ERR_INVALID_ARGUMENT, "empty scene");
+  const uint32_t accel = d->flags & RT_FLAG_ACCEL_MASK;
+  if (accel > RT_ACCEL_BRUTE) return fail(RT_ERR_INVALID_ARGUMENT, "unknown accel flag");
+  for (uint32_t i = 0; i < d->n_meshes; i++) {
+    const rt_mesh_desc& m = d->meshes[i];
+    if ((m.n_triangles && (!m.indices || !m.vertices)) || (m.n_vertices && !m.vertices)) return fail(RT_ERR_INVALID_ARGUMENT, "null mesh buffer");
+    for (size_t k = 0; k < 3 * (size_t)m.n_triangles; k++)
+      if (m.indices[k] >= m.n_vertices) return fail(RT_ERR_INVALID_ARGUMENT, "mesh index out of range");
+  }
+  for (uint32_t i = 0; i < d->n_instances; i++)
+    if (d->instances[i].mesh >= d->n_meshes) return fail(RT_ERR_INVALID_ARGUMENT, "instance references unknown mesh");
+  if (rt_device_count() == 0) return fail(RT_ERR_NO_DEVICE, "no CUDA device: librt_b200 has no CPU fallback");
+  int dev = d->device_id;
+  if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) return fail(RT_ERR_NO_DEVICE, "cudaGetDevice failed"); }
+  RT_CUDA_TRY(cudaSetDevice(dev), g_err);
+
+  std::unique_ptr<Scene, void (*)(Scene*)> s(new Scene(), destroy_scene);
+  s->device = dev;
+  s->accel = accel;
+  s->pipe = pipeline_create();
+  cudaEvent_t e0, e1;
+  RT_CUDA_TRY(cudaEventCreate(&e0), g_err);
+  RT_CUDA_TRY(cudaEventCreate(&e1), g_err);
+  s->blas.resize(d->n_meshes);
+  // upload geometry first (not part of build_ms, like the reference's buffer creation)
+  for (uint32_t i = 0; i < d->n_meshes; i++) {
+    const rt_mesh_desc& m = d->meshes[i];
+    BlasHost& b = s->blas[i];
+    if (m.n_vertices) {
+      RT_CUDA_TRY(cudaMalloc(&b.d_verts, (size_t)m.n_vertices * 24), g_err);
+      RT_CUDA_TRY(cudaMemcpy(b.d_verts, m.vertices, (size_t)m.n_vertices * 24, cudaMemcpyHostToDevice), g_err);
+    }
+    if (m.n_triangles) {
+      RT_CUDA_TRY(cudaMalloc(&b.d_idx, (size_t)m.n_triangles * 12), g_err);
+      RT_CUDA_TRY(cudaMemcpy(b.d_idx, m.indices, (size_t)m.n_triangles * 12, cudaMemcpyHostToDevice), g_err);
+    }
+  }
+  RT_CUDA_TRY(cudaEventRecord(e0, s->stream), g_err);
+  for (uint32_t i = 0; i < d->n_meshes; i++) {
+    int rc = build_blas(s->blas[i], d->meshes[i].n_vertices, d->meshes[i].n_triangles, (int)accel, s->stream, g_err);
+    if (rc != RT_OK) return rc;
+  }
+  RT_CUDA_TRY(cudaEventRecord(e1, s->stream), g_err);
+  RT_CUDA_TRY(cudaEventSynchronize(e1), g_err);
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  s->stats.build_ms = ms;
+
+  std::vector<BlasDev> hb(d->n_meshes);
+  for (uint32_t i = 0; i < d->n_meshes; i++) {
+    hb[i] = s->blas[i].dev;
+    s->stats.bvh_nodes += s->blas[i].node_count;
+    s->stats.bvh_bytes += s->blas[i].bytes;
+  }
+  s->stats.node_bytes = accel == ACCEL_WIDE ? 80 : (accel == ACCEL_BVH2 ? 64 : 0);
+  s->stats.tri_bytes = 48;
+  RT_CUDA_TRY(cudaMalloc(&s->d_blas, hb.size() * sizeof(BlasDev)), g_err);
+  RT_CUDA_TRY(cudaMemcpy(s->d_blas, hb.data(), hb.size() * sizeof(BlasDev), cudaMemcpyHostToDevice), g_err);
+
+  s->inst.resize(d->n_instances);
+  if (d->n_instances) {
+    RT_CUDA_TRY(cudaMalloc(&s->d_inst, d->n_instances * sizeof(InstDev)), g_err);
+    for (uint32_t i = 0; i < d->n_instances; i++) {
+      s->inst[i].mesh = d->instances[i].mesh;
+      s->inst[i].type = d->instances[i].type;
+      set_instance(*s, i, d->instances[i].transform);
+    }
+    int rc = upload_instances(*s);
+    if (rc != RT_OK) return rc;
+  }
+  if (d->skybox_rgba8 && d->sky_w && d->sky_h) {
+    const size_t bytes = (size_t)6 * d->sky_w * d->sky_h * 4;
+    RT_CUDA_TRY(cudaMalloc(&s->d_sky, bytes), g_err);
+    RT_CUDA_TRY(cudaMemcpy(s->d_sky, d->skybox_rgba8, bytes, cudaMemcpyHostToDevice), g_err);
+    s->sky_w = d->sky_w;
+    s->sky_h = d->sky_h;
+  }
+  *out_scene = s.release();
+  return RT_OK;
+}
+
+int rt_scene_set_transforms(void* scene, const float* xforms12, uint32_t n) {
+  Scene* s = (Scene*)scene;
+  if (!s || !xforms12 || n != s->inst.size()) return fail(RT_ERR_INVALID_ARGUMENT, "bad transforms");
+  RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
+  for (uint32_t i = 0; i < n; i++) set_instance(*s, i, xforms12 + 12 * (size_t)i);
+  return upload_instances(*s);
+}
+
+int rt_scene_destroy(void* scene) {
+  destroy_scene((Scene*)scene);
+  return RT_OK;
+}
+
+int rt_scene_set_stream(void* scene, void* stream) {
+  if (!scene) return fail(RT_ERR_INVALID_ARGUMENT, "null scene");
+  ((Scene*)scene)->stream = (cudaStream_t)stream;
+  return RT_OK;
+}
+
+int rt_set_counting(void* scene, int enable) {
+  if (!scene) return fail(RT_ERR_INVALID_ARGUMENT, "null scene");
+  ((Scene*)scene)->counting = enable != 0;
+  return RT_OK;
+}
+
+uint64_t rt_frame_shard_pixels(const rt_frame_params* p) { return p ? shard_pixels(p) : 0; }
+
+uint64_t rt_frame_output_bytes(const rt_frame_params* p) {
+  if (!p) return 0;
+  const uint64_t px = (p->shard_count > 1) ? shard_pixels(p) : (uint64_t)p->width * p->height;
+  return px * (p->output_format == RT_FORMAT_RGBA8 ? 4 : 16);
+}
+
+static int render_common(Scene* s, const rt_camera* cam, const rt_frame_params* p, void* out, rt_hit* d_primary) {
+  FrameRequest rq{};
+  int rc = fill_uniforms(cam, p, rq.U);
+  if (rc != RT_OK) return rc;
+  RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
+  rq.scene = s->dev();
+  rq.output_format = p->output_format;
+  rq.counting = s->counting;
+  rq.want_primary = d_primary != nullptr;
+  rq.d_primary = d_primary;
+  const size_t bytes = (size_t)rt_frame_output_bytes(p);
+  if (out) {
+    if (p->output_location == RT_LOCATION_DEVICE) {
+      rq.d_out = out;
+    } else {
+      if (bytes > s->d_out_bytes) {
+        cudaFree(s->d_out);
+        s->d_out = nullptr;
+        s->d_out_bytes = 0;
+        RT_CUDA_TRY(cudaMalloc(&s->d_out, bytes), g_err);
+        s->d_out_bytes = bytes;
+      }
+      rq.d_out = s->d_out;
+    }
+  }
+  rc = pipeline_render(s->pipe, rq, s->stream, &s->stats, g_err);
+  if (rc != RT_OK) return rc;
+  if (out && p->output_location == RT_LOCATION_HOST) {
+    RT_CUDA_TRY(cudaMemcpyAsync(out, s->d_out, bytes, cudaMemcpyDeviceToHost, s->stream), g_err);
+    RT_CUDA_TRY(cudaStreamSynchronize(s->stream), g_err);
+  }
+  return RT_OK;
+}
+
+int rt_render_frame(void* scene, const rt_camera* cam, const rt_frame_params* p, void* rgba_out) {
+  Scene* s = (Scene*)scene;
+  if (!s || !rgba_out) return fail(RT_ERR_INVALID_ARGUMENT, "null scene or output");
+  return render_common(s, cam, p, rgba_out, nullptr);
+}
+
+int rt_assemble_shards(void* scene, const rt_frame_params* p, const void* gathered, void* frame_out) {
+  Scene* s = (Scene*)scene;
+  if (!s || !p || !gathered || !frame_out) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  rt_camera cam{};
+  FrameUniforms U;
+  int rc = fill_uniforms(&cam, p, U);
+  if (rc != RT_OK) return rc;
+  RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
+  rc = assemble_shards(U, p->output_format, gathered, frame_out, s->stream, g_err);
+  if (rc != RT_OK) return rc;
+  RT_CUDA_TRY(cudaStreamSynchronize(s->stream), g_err);
+  return RT_OK;
+}
+
+int rt_primary_hits(void* scene, const rt_camera* cam, const rt_frame_params* p, rt_hit* hits_out) {
+  Scene* s = (Scene*)scene;
+  if (!s || !p || !hits_out) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  if (p->shard_count > 1) return fail(RT_ERR_UNSUPPORTED, "primary hits are exported for full frames only");
+  RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
+  const size_t n = (size_t)p->width * p->height * p->samples_per_pixel;
+  rt_hit* d = nullptr;
+  RT_CUDA_TRY(cudaMalloc(&d, n * sizeof(rt_hit)), g_err);
+  rt_frame_params q = *p;
+  q.max_bounce_count = 0;  // only the first trace of every sample is needed
+  int rc = render_common(s, cam, &q, nullptr, d);
+  if (rc == RT_OK) {
+    cudaError_t e = cudaMemcpy(hits_out, d, n * sizeof(rt_hit), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) rc = fail(RT_ERR_CUDA, cudaGetErrorString(e));
+  }
+  cudaFree(d);
+  return rc;
+}
+
+int rt_trace_rays(void* scene, uint64_t n, const float* origins, const float* dirs, float tmin, float tmax, int any_hit,
+                  rt_hit* hits_out) {
+  Scene* s = (Scene*)scene;
+  if (!s || (n && (!origins || !dirs || !hits_out))) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  if (n == 0) return RT_OK;
+  RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
+  float *d_o = nullptr, *d_d = nullptr;
+  rt_hit* d_h = nullptr;
+  int rc = RT_OK;
+  auto cleanup = [&]() { cudaFree(d_o); cudaFree(d_d); cudaFree(d_h); };
+  cudaError_t e;
+  if ((e = cudaMalloc(&d_o, n * 12)) != cudaSuccess || (e = cudaMalloc(&d_d, n * 12)) != cudaSuccess ||
+      (e = cudaMalloc(&d_h, n * sizeof(rt_hit))) != cudaSuccess ||
+      (e = cudaMemcpy(d_o, origins, n * 12, cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(d_d, dirs, n * 12, cudaMemcpyHostToDevice)) != cudaSuccess) {
+    cleanup();
+    return fail(RT_ERR_CUDA, cudaGetErrorString(e));
+  }
+  rc = pipeline_trace_batch(s->pipe, s->dev(), n, d_o, d_d, tmin, tmax, any_hit != 0, s->counting, d_h, s->stream,
+                            &s->stats, g_err);
+  if (rc == RT_OK && (e = cudaMemcpy(hits_out, d_h, n * sizeof(rt_hit), cudaMemcpyDeviceToHost)) != cudaSuccess)
+    rc = fail(RT_ERR_CUDA, cudaGetErrorString(e));
+  cleanup();
+  return rc;
+}
+
+int rt_get_stats(void* scene, rt_stats* out) {
+  if (!scene || !out) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  *out = ((Scene*)scene)->stats;
+  return RT_OK;
+}
+
+int rt_debug_sort_pairs(int device_id, uint64_t n, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                        uint32_t* vals_out) {
+  if (n && (!keys_in || !vals_in || !keys_out || !vals_out)) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  if (rt_device_count() == 0) return fail(RT_ERR_NO_DEVICE, "no CUDA device: librt_b200 has no CPU fallback");
+  if (n == 0) return RT_OK;
+  RT_CUDA_TRY(cudaSetDevice(device_id < 0 ? 0 : device_id), g_err);
+  uint64_t *k = nullptr, *ka = nullptr;
+  uint32_t *v = nullptr, *va = nullptr, *h = nullptr;
+  auto cleanup = [&]() { cudaFree(k); cudaFree(ka); cudaFree(v); cudaFree(va); cudaFree(h); };
+  cudaError_t e;
+  if ((e = cudaMalloc(&k, n * 8)) != cudaSuccess || (e = cudaMalloc(&ka, n * 8)) != cudaSuccess ||
+      (e = cudaMalloc(&v, n * 4)) != cudaSuccess || (e = cudaMalloc(&va, n * 4)) != cudaSuccess ||
+      (e = cudaMalloc(&h, sort_hist_words(n) * 4)) != cudaSuccess ||
+      (e = cudaMemcpy(k, keys_in, n * 8, cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(v, vals_in, n * 4, cudaMemcpyHostToDevice)) != cudaSuccess) {
+    cleanup();
+    return fail(RT_ERR_CUDA, cudaGetErrorString(e));
+  }
+  int rc = sort_pairs(k, ka, v, va, n, 64, h, nullptr, g_err);
+  if (rc == RT_OK) {
+    if ((e = cudaMemcpy(keys_out, k, n * 8, cudaMemcpyDeviceToHost)) != cudaSuccess ||
+        (e = cudaMemcpy(vals_out, v, n * 4, cudaMemcpyDeviceToHost)) != cudaSuccess)
+      rc = fail(RT_ERR_CUDA, cudaGetErrorString(e));
+  }
+  cleanup();
+  return rc;
+}
+
+}  // extern "C"

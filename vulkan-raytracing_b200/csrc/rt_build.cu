@@ -1,0 +1,403 @@
+// rt_build.cu — GPU acceleration-structure build for sm_100a: kernels around the
+// per-element functions of rt_build.cuh plus the radix sort.  Replaces the driver work
+// behind vkCmdBuildAccelerationStructuresKHR in buildBLAS (main.cpp:463-536).
+//
+// HBM traffic per triangle (the builder is bandwidth-bound integer/byte work, no tensor
+// cores): boxes 32 B w + 32 B r, key/value sort 8 passes x (12 B r + 12 B w) + histogram
+// 8 x 8 B r, tree arrays ~40 B, box fit ~96 B, wide emit 48 B (triangle) + ~25 B (node).
+#include <algorithm>
+#include <cstdio>
+
+#include "rt_build.cuh"
+#include "rt_internal.h"
+
+namespace rt {
+
+static int g_sm_count = 0;
+int sm_count() {
+  if (!g_sm_count) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sm_count <= 0) g_sm_count = 148;
+  }
+  return g_sm_count;
+}
+
+// ------------------------------------------------------------------------------------------
+// radix sort: 8-bit digits, per pass: tile histograms -> per-digit scan over tiles -> stable
+// scatter (warp match ranking).  Tile = 256 threads x 16 keys.
+// ------------------------------------------------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
+
+size_t sort_hist_words(uint64_t n) { return 256 * ((n + SORT_TILE - 1) / SORT_TILE) + 256; }
+
+__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const uint64_t* __restrict__ keys, uint64_t n, int shift,
+                                                            uint32_t* __restrict__ hist, uint32_t num_tiles) {
+  __shared__ uint32_t sh[256];
+  const uint32_t tile = blockIdx.x;
+  sh[threadIdx.x] = 0;
+  __syncthreads();
+  const uint64_t base = (uint64_t)tile * SORT_TILE;
+#pragma unroll 4
+  for (int r = 0; r < SORT_ITEMS; r++) {
+    const uint64_t p = base + (uint64_t)r * SORT_THREADS + threadIdx.x;
+    if (p < n) atomicAdd(&sh[(uint32_t)(keys[p] >> shift) & 0xFFu], 1u);
+  }
+  __syncthreads();
+  hist[(size_t)threadIdx.x * num_tiles + tile] = sh[threadIdx.x];
+}
+
+// one block per digit: exclusive scan of that digit's counts over all tiles
+__global__ void __launch_bounds__(256) k_sort_scan(uint32_t* __restrict__ hist, uint32_t num_tiles,
+                                                   uint32_t* __restrict__ totals) {
+  __shared__ uint32_t warp_sum[8];
+  __shared__ uint32_t carry_s;
+  uint32_t* row = hist + (size_t)blockIdx.x * num_tiles;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < num_tiles; base += 256) {
+    const uint32_t i = base + threadIdx.x;
+    const uint32_t v = i < num_tiles ? row[i] : 0u;
+    uint32_t x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) warp_sum[wid] = x;
+    __syncthreads();
+    uint32_t wbase = 0;
+    for (int w = 0; w < wid; w++) wbase += warp_sum[w];
+    const uint32_t carry = carry_s;
+    if (i < num_tiles) row[i] = carry + wbase + x - v;
+    __syncthreads();
+    if (threadIdx.x == 255) carry_s = carry + wbase + x;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) totals[blockIdx.x] = carry_s;
+}
+
+__global__ void __launch_bounds__(SORT_THREADS)
+    k_sort_scatter(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout,
+                   uint32_t* __restrict__ vout, uint64_t n, int shift, const uint32_t* __restrict__ hist,
+                   const uint32_t* __restrict__ totals, uint32_t num_tiles) {
+  __shared__ uint32_t warp_cnt[SORT_THREADS / 32][256];
+  __shared__ uint32_t digit_base[256];
+  __shared__ uint32_t wsum[8];
+  const uint32_t tile = blockIdx.x;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  // exclusive scan of the 256 digit totals -> global start of each digit
+  {
+    const uint32_t v = totals[threadIdx.x];
+    uint32_t x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) wsum[wid] = x;
+    for (int w = 0; w < SORT_THREADS / 32; w++) warp_cnt[w][threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t wb = 0;
+    for (int w = 0; w < wid; w++) wb += wsum[w];
+    digit_base[threadIdx.x] = wb + x - v + hist[(size_t)threadIdx.x * num_tiles + tile];
+  }
+  __syncthreads();
+  uint64_t key[SORT_ITEMS];
+  uint32_t val[SORT_ITEMS];
+  uint32_t rank[SORT_ITEMS];
+  const uint64_t base = (uint64_t)tile * SORT_TILE + (uint64_t)wid * (SORT_ITEMS * 32) + lane;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+  for (int r = 0; r < SORT_ITEMS; r++) {
+    const uint64_t p = base + (uint64_t)r * 32;
+    const bool valid = p < n;
+    key[r] = valid ? kin[p] : 0ull;
+    val[r] = valid ? vin[p] : 0u;
+  }
+#pragma unroll
+  for (int r = 0; r < SORT_ITEMS; r++) {
+    const uint64_t p = base + (uint64_t)r * 32;
+    const bool valid = p < n;
+    const uint32_t d = valid ? ((uint32_t)(key[r] >> shift) & 0xFFu) : 0x100u;
+    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, d);
+    const uint32_t prior = valid ? warp_cnt[wid][d] : 0u;
+    __syncwarp();
+    const uint32_t before = __popc(peers & lt_mask);
+    if (valid && before == 0) warp_cnt[wid][d] = prior + __popc(peers);
+    __syncwarp();
+    rank[r] = prior + before;
+  }
+  __syncthreads();
+  {  // exclusive scan over warps, per digit
+    uint32_t run = 0;
+    for (int w = 0; w < SORT_THREADS / 32; w++) {
+      const uint32_t c = warp_cnt[w][threadIdx.x];
+      warp_cnt[w][threadIdx.x] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < SORT_ITEMS; r++) {
+    const uint64_t p = base + (uint64_t)r * 32;
+    if (p < n) {
+      const uint32_t d = (uint32_t)(key[r] >> shift) & 0xFFu;
+      const uint32_t dst = digit_base[d] + warp_cnt[wid][d] + rank[r];
+      kout[dst] = key[r];
+      vout[dst] = val[r];
+    }
+  }
+}
+
+int sort_pairs(uint64_t* keys, uint64_t* keys_alt, uint32_t* vals, uint32_t* vals_alt, uint64_t n, int key_bits,
+               uint32_t* hist, cudaStream_t stream, std::string& err) {
+  if (n == 0) return RT_OK;
+  if (n > 0xFFFFFFFFull) { err = "sort_pairs: n exceeds 32-bit positions"; return RT_ERR_UNSUPPORTED; }
+  const uint32_t num_tiles = (uint32_t)((n + SORT_TILE - 1) / SORT_TILE);
+  int passes = (key_bits + 7) / 8;
+  if (passes & 1) passes++;  // even number of passes: the result lands in keys/vals
+  uint32_t* totals = hist + (size_t)256 * num_tiles;
+  uint64_t* kin = keys; uint64_t* kout = keys_alt;
+  uint32_t* vin = vals; uint32_t* vout = vals_alt;
+  for (int p = 0; p < passes; p++) {
+    const int shift = 8 * p;
+    k_sort_hist<<<num_tiles, SORT_THREADS, 0, stream>>>(kin, n, shift, hist, num_tiles);
+    k_sort_scan<<<256, 256, 0, stream>>>(hist, num_tiles, totals);
+    k_sort_scatter<<<num_tiles, SORT_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, hist, totals, num_tiles);
+    std::swap(kin, kout);
+    std::swap(vin, vout);
+  }
+  RT_CUDA_TRY(cudaGetLastError(), err);
+  return RT_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// build kernels
+// ------------------------------------------------------------------------------------------
+__global__ void k_init_bounds(uint32_t* bounds) {
+  const int i = threadIdx.x;
+  if (i < 12) bounds[i] = ((i % 6) < 3) ? 0xFFFFFFFFu : 0u;
+}
+
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xFFFFFFFFu, v, o));
+  return v;
+}
+
+__global__ void __launch_bounds__(256) k_tri_boxes(BuildArrays a) {
+  const float INF = __int_as_float(0x7f800000);
+  float lo[3] = {INF, INF, INF}, hi[3] = {-INF, -INF, -INF}, clo[3] = {INF, INF, INF}, chi[3] = {-INF, -INF, -INF};
+  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < a.ntri; t += gridDim.x * blockDim.x) {
+    f3 l, h;
+    tri_box(a, t, l, h);
+    a.tri_lo[t] = make_float4(l.x, l.y, l.z, 0.0f);
+    a.tri_hi[t] = make_float4(h.x, h.y, h.z, 0.0f);
+    const float c[3] = {0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)};
+    const float ll[3] = {l.x, l.y, l.z}, hh[3] = {h.x, h.y, h.z};
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      lo[k] = fminf(lo[k], ll[k]); hi[k] = fmaxf(hi[k], hh[k]);
+      clo[k] = fminf(clo[k], c[k]); chi[k] = fmaxf(chi[k], c[k]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const float m0 = warp_min(lo[k]), m1 = warp_max(hi[k]), m2 = warp_min(clo[k]), m3 = warp_max(chi[k]);
+    if ((threadIdx.x & 31) == 0) {
+      atomicMin(&a.bounds[k], float_to_ordered(m0));
+      atomicMax(&a.bounds[3 + k], float_to_ordered(m1));
+      atomicMin(&a.bounds[6 + k], float_to_ordered(m2));
+      atomicMax(&a.bounds[9 + k], float_to_ordered(m3));
+    }
+  }
+}
+
+// pad = 4e-6 * max |coordinate| of the mesh: the margin that keeps box culling
+// conservative with respect to the watertight triangle test
+__device__ __forceinline__ float mesh_pad(const uint32_t* bounds) {
+  float amax = 0.0f;
+#pragma unroll
+  for (int k = 0; k < 6; k++) amax = fmaxf(amax, fabsf(ordered_to_float(bounds[k])));
+  return amax * 4e-6f + 1e-30f;
+}
+
+__global__ void __launch_bounds__(256) k_morton(BuildArrays a) {
+  const float pad = mesh_pad(a.bounds);
+  const f3 cmin = mk3(ordered_to_float(a.bounds[6]), ordered_to_float(a.bounds[7]), ordered_to_float(a.bounds[8]));
+  const f3 cmax = mk3(ordered_to_float(a.bounds[9]), ordered_to_float(a.bounds[10]), ordered_to_float(a.bounds[11]));
+  const f3 cinv = mk3(cmax.x > cmin.x ? 1.0f / (cmax.x - cmin.x) : 0.0f, cmax.y > cmin.y ? 1.0f / (cmax.y - cmin.y) : 0.0f,
+                      cmax.z > cmin.z ? 1.0f / (cmax.z - cmin.z) : 0.0f);
+  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < a.ntri; t += gridDim.x * blockDim.x) {
+    float4 l = a.tri_lo[t], h = a.tri_hi[t];
+    const f3 c = mk3(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z));
+    a.keys[t] = morton63(c, cmin, cinv);
+    a.vals[t] = t;
+    l.x -= pad; l.y -= pad; l.z -= pad;
+    h.x += pad; h.y += pad; h.z += pad;
+    a.tri_lo[t] = l;
+    a.tri_hi[t] = h;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_karras(BuildArrays a) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i + 1 < a.ntri; i += gridDim.x * blockDim.x)
+    karras_node(a, (int)i);
+}
+
+__global__ void __launch_bounds__(256) k_refit(BuildArrays a) {
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < a.ntri; j += gridDim.x * blockDim.x)
+    refit_from_leaf(a, j);
+}
+
+__global__ void __launch_bounds__(128) k_collapse(BuildArrays a, uint32_t begin, uint32_t end) {
+  for (uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x; w < end; w += gridDim.x * blockDim.x)
+    collapse_node(a, w);
+}
+
+__global__ void __launch_bounds__(256) k_emit_bvh2(BuildArrays a, float4* nodes, float4* tris) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.ntri; i += gridDim.x * blockDim.x) {
+    if (i + 1 < a.ntri) emit_bvh2_node(a, (int)i, nodes);
+    emit_tri(a, i, a.vals[i], tris);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_emit_brute(BuildArrays a, float4* tris) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.ntri; i += gridDim.x * blockDim.x)
+    emit_tri(a, i, i, tris);
+}
+
+__global__ void k_set_root(uint32_t* work, uint32_t* counters) {
+  work[0] = 0u;
+  counters[0] = 1u;
+  counters[1] = 0u;
+}
+
+static int grid_for(uint64_t n, int block) {
+  const uint64_t want = (n + block - 1) / block;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  return (int)std::max<uint64_t>(1, std::min(want, cap));
+}
+
+struct TempAlloc {
+  std::vector<void*> ptrs;
+  ~TempAlloc() { for (void* p : ptrs) cudaFree(p); }
+  template <class T> cudaError_t get(T** p, size_t count) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+    if (e == cudaSuccess) { ptrs.push_back(q); *p = (T*)q; }
+    return e;
+  }
+};
+
+void free_blas(BlasHost& b) {
+  cudaFree(b.d_verts); cudaFree(b.d_idx); cudaFree(b.d_nodes); cudaFree(b.d_tris);
+  b = BlasHost{};
+}
+
+int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, cudaStream_t stream, std::string& err) {
+  b.dev.verts = b.d_verts;
+  b.dev.idx = b.d_idx;
+  b.dev.ntri = ntri;
+  b.dev.nodes = nullptr;
+  b.dev.tris = nullptr;
+  b.dev.nnodes = 0;
+  b.node_count = 0;
+  b.bytes = 0;
+  if (ntri == 0) return RT_OK;
+  const size_t N = ntri;
+  TempAlloc tmp;
+  BuildArrays a{};
+  a.verts = b.d_verts;
+  a.idx = b.d_idx;
+  a.ntri = ntri;
+  uint64_t* keys_alt = nullptr;
+  uint32_t* vals_alt = nullptr;
+  uint32_t* hist = nullptr;
+  RT_CUDA_TRY(tmp.get(&a.tri_lo, N), err);
+  RT_CUDA_TRY(tmp.get(&a.tri_hi, N), err);
+  RT_CUDA_TRY(tmp.get(&a.bounds, 16), err);
+  RT_CUDA_TRY(cudaMalloc(&b.d_tris, N * 48), err);
+  k_init_bounds<<<1, 32, 0, stream>>>(a.bounds);
+  k_tri_boxes<<<grid_for(N, 256), 256, 0, stream>>>(a);
+  if (accel != ACCEL_BRUTE) {
+    RT_CUDA_TRY(tmp.get(&a.keys, N), err);
+    RT_CUDA_TRY(tmp.get(&keys_alt, N), err);
+    RT_CUDA_TRY(tmp.get(&a.vals, N), err);
+    RT_CUDA_TRY(tmp.get(&vals_alt, N), err);
+    RT_CUDA_TRY(tmp.get(&hist, sort_hist_words(N)), err);
+    RT_CUDA_TRY(tmp.get(&a.parent, 2 * N), err);
+    RT_CUDA_TRY(tmp.get(&a.left, N), err);
+    RT_CUDA_TRY(tmp.get(&a.right, N), err);
+    RT_CUDA_TRY(tmp.get(&a.first, N), err);
+    RT_CUDA_TRY(tmp.get(&a.node_lo, 2 * N), err);
+    RT_CUDA_TRY(tmp.get(&a.node_hi, 2 * N), err);
+    RT_CUDA_TRY(tmp.get(&a.flags, N), err);
+    RT_CUDA_TRY(cudaMemsetAsync(a.flags, 0, N * sizeof(uint32_t), stream), err);
+    k_morton<<<grid_for(N, 256), 256, 0, stream>>>(a);
+    int rc = sort_pairs(a.keys, keys_alt, a.vals, vals_alt, N, 63, hist, stream, err);
+    if (rc != RT_OK) return rc;
+    if (ntri > 1) k_karras<<<grid_for(N, 256), 256, 0, stream>>>(a);
+    k_refit<<<grid_for(N, 256), 256, 0, stream>>>(a);
+  }
+  RT_CUDA_TRY(cudaGetLastError(), err);
+
+  if (accel == ACCEL_WIDE) {
+    uint4* wide_tmp = nullptr;
+    RT_CUDA_TRY(tmp.get(&wide_tmp, 5 * N), err);   // worst case one wide node per triangle
+    RT_CUDA_TRY(tmp.get(&a.work, N), err);
+    RT_CUDA_TRY(tmp.get(&a.counters, 4), err);
+    a.wide = wide_tmp;
+    a.tris = (float4*)b.d_tris;
+    k_set_root<<<1, 1, 0, stream>>>(a.work, a.counters);
+    uint32_t begin = 0, end = 1;
+    while (begin < end) {
+      k_collapse<<<grid_for(end - begin, 128), 128, 0, stream>>>(a, begin, end);
+      uint32_t counters[2];
+      RT_CUDA_TRY(cudaMemcpyAsync(counters, a.counters, sizeof counters, cudaMemcpyDeviceToHost, stream), err);
+      RT_CUDA_TRY(cudaStreamSynchronize(stream), err);
+      begin = end;
+      end = counters[0];
+      if (end > N) { err = "wide node overflow"; return RT_ERR_CUDA; }
+    }
+    b.node_count = end;
+    RT_CUDA_TRY(cudaMalloc(&b.d_nodes, (size_t)end * 80), err);
+    RT_CUDA_TRY(cudaMemcpyAsync(b.d_nodes, wide_tmp, (size_t)end * 80, cudaMemcpyDeviceToDevice, stream), err);
+    b.bytes = (uint64_t)end * 80 + N * 48;
+  } else if (accel == ACCEL_BVH2) {
+    RT_CUDA_TRY(cudaMalloc(&b.d_nodes, std::max<size_t>(N - 1, 1) * 64), err);
+    k_emit_bvh2<<<grid_for(N, 256), 256, 0, stream>>>(a, (float4*)b.d_nodes, (float4*)b.d_tris);
+    b.node_count = N - 1;
+    b.bytes = (uint64_t)(N - 1) * 64 + N * 48;
+  } else {
+    k_emit_brute<<<grid_for(N, 256), 256, 0, stream>>>(a, (float4*)b.d_tris);
+    b.bytes = N * 48;
+  }
+  uint32_t hb[12];
+  RT_CUDA_TRY(cudaMemcpyAsync(hb, a.bounds, sizeof hb, cudaMemcpyDeviceToHost, stream), err);
+  RT_CUDA_TRY(cudaStreamSynchronize(stream), err);
+  RT_CUDA_TRY(cudaGetLastError(), err);
+  float amax = 0.0f;
+  for (int k = 0; k < 6; k++) amax = std::max(amax, std::fabs(ordered_to_float(hb[k])));
+  const float pad = amax * 4e-6f + 1e-30f;
+  for (int k = 0; k < 3; k++) {
+    b.lo[k] = ordered_to_float(hb[k]) - pad;
+    b.hi[k] = ordered_to_float(hb[3 + k]) + pad;
+  }
+  b.dev.nodes = (const float4*)b.d_nodes;
+  b.dev.tris = (const float4*)b.d_tris;
+  b.dev.nnodes = (uint32_t)b.node_count;
+  return RT_OK;
+}
+
+}  // namespace rt

@@ -1,0 +1,327 @@
+// rt_build.cuh — per-element functions of the acceleration-structure build: what
+// vkCmdBuildAccelerationStructuresKHR does inside the driver for the reference's
+// buildBLAS (main.cpp:463-536).  Pipeline (kernels in rt_build.cu):
+//   triangle boxes + centroid bounds -> 63-bit Morton codes -> radix sort ->
+//   Karras 2012 binary radix tree -> bottom-up box fit -> surface-area guided collapse
+//   into compressed 8-wide nodes (80 B) + leaf triangle array.
+// RT_HD so tests/emu can run the same code serially on the CPU.
+#pragma once
+#include "rt_trav.cuh"
+
+#if defined(__CUDA_ARCH__)
+#define RT_ATOMIC_ADD(p, v) atomicAdd((p), (v))
+#define RT_FENCE() __threadfence()
+#define RT_LDCG(p) __ldcg(p)
+#else
+namespace rt {
+template <class T> inline T emu_atomic_add(T* p, T v) { T o = *p; *p = o + v; return o; }
+}
+#define RT_ATOMIC_ADD(p, v) rt::emu_atomic_add((p), (v))
+#define RT_FENCE() ((void)0)
+#define RT_LDCG(p) (*(p))
+#endif
+
+namespace rt {
+
+// Everything the build of one mesh reads and writes (device pointers).
+struct BuildArrays {
+  // inputs
+  const float* verts;     // stride 6
+  const uint32_t* idx;    // 3 per triangle
+  uint32_t ntri;
+  // per triangle (original order)
+  float4* tri_lo;         // padded box min (w unused)
+  float4* tri_hi;
+  // bounds[0..2] = min, [3..5] = max of triangle boxes; [6..8],[9..11] = of centroids;
+  // all stored as order-preserving uint32 for atomicMin/Max
+  uint32_t* bounds;
+  uint64_t* keys;         // Morton codes (sorted in place by the radix sort)
+  uint32_t* vals;         // triangle ids in Morton order
+  // binary radix tree: internal nodes [0, ntri-1), leaf j has id (ntri-1)+j
+  int32_t* parent;        // [2*ntri-1]
+  int32_t* left;          // [ntri-1]
+  int32_t* right;         // [ntri-1]
+  uint32_t* first;        // [ntri-1] first leaf covered
+  float4* node_lo;        // [2*ntri-1] xyz = box min, w = leaf count (as uint bits)
+  float4* node_hi;        // [2*ntri-1]
+  uint32_t* flags;        // [ntri-1] arrival counters of the bottom-up pass
+  // wide output
+  uint4* wide;            // 5 x uint4 per node
+  float4* tris;           // 3 x float4 per leaf triangle
+  uint32_t* work;         // [max wide nodes] binary node id behind each wide node
+  uint32_t* counters;     // [0] wide nodes allocated, [1] leaf triangles allocated
+};
+
+RT_HD uint32_t float_to_ordered(float f) {
+  uint32_t u = f2u(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+RT_HD float ordered_to_float(uint32_t o) {
+  return u2f((o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o);
+}
+
+RT_HD f3 load_pos(const float* verts, uint32_t v) {
+  const float* p = verts + 6 * (size_t)v;
+  return mk3(RT_LDG(p), RT_LDG(p + 1), RT_LDG(p + 2));
+}
+
+// box of one triangle (unpadded)
+RT_HD void tri_box(const BuildArrays& a, uint32_t t, f3& lo, f3& hi) {
+  const f3 p0 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)t]));
+  const f3 p1 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)t + 1]));
+  const f3 p2 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)t + 2]));
+  lo = mk3(fminf(p0.x, fminf(p1.x, p2.x)), fminf(p0.y, fminf(p1.y, p2.y)), fminf(p0.z, fminf(p1.z, p2.z)));
+  hi = mk3(fmaxf(p0.x, fmaxf(p1.x, p2.x)), fmaxf(p0.y, fmaxf(p1.y, p2.y)), fmaxf(p0.z, fmaxf(p1.z, p2.z)));
+}
+
+RT_HD uint64_t expand21(uint32_t v) {  // spread 21 bits to every third bit
+  uint64_t x = v & 0x1FFFFFu;
+  x = (x | (x << 32)) & 0x1F00000000FFFFull;
+  x = (x | (x << 16)) & 0x1F0000FF0000FFull;
+  x = (x | (x << 8)) & 0x100F00F00F00F00Full;
+  x = (x | (x << 4)) & 0x10C30C30C30C30C3ull;
+  x = (x | (x << 2)) & 0x1249249249249249ull;
+  return x;
+}
+
+// 63-bit Morton code of a centroid inside the centroid bounds
+RT_HD uint64_t morton63(f3 c, f3 cmin, f3 cinv) {
+  const float s = 2097152.0f;  // 2^21
+  float x = (c.x - cmin.x) * cinv.x * s, y = (c.y - cmin.y) * cinv.y * s, z = (c.z - cmin.z) * cinv.z * s;
+  x = fminf(fmaxf(x, 0.0f), 2097151.0f);
+  y = fminf(fmaxf(y, 0.0f), 2097151.0f);
+  z = fminf(fmaxf(z, 0.0f), 2097151.0f);
+  return (expand21((uint32_t)x) << 2) | (expand21((uint32_t)y) << 1) | expand21((uint32_t)z);
+}
+
+// Karras 2012: common-prefix length of sorted keys i and j, index as tie-break
+RT_HD int karras_delta(const uint64_t* keys, int n, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  const uint64_t a = RT_LDG(&keys[i]), b = RT_LDG(&keys[j]);
+  if (a == b) return 64 + clz32((uint32_t)i ^ (uint32_t)j);
+  return clz64(a ^ b);
+}
+
+// one internal node of the binary radix tree
+RT_HD void karras_node(const BuildArrays& a, int i) {
+  const int n = (int)a.ntri;
+  const uint64_t* k = a.keys;
+  const int d = (karras_delta(k, n, i, i + 1) - karras_delta(k, n, i, i - 1)) >= 0 ? 1 : -1;
+  const int dmin = karras_delta(k, n, i, i - d);
+  int lmax = 2;
+  while (karras_delta(k, n, i, i + lmax * d) > dmin) lmax *= 2;
+  int l = 0;
+  for (int t = lmax / 2; t >= 1; t /= 2)
+    if (karras_delta(k, n, i, i + (l + t) * d) > dmin) l += t;
+  const int j = i + l * d;
+  const int dnode = karras_delta(k, n, i, j);
+  int s = 0;
+  int t = l;
+  do {
+    t = (t + 1) >> 1;
+    if (karras_delta(k, n, i, i + (s + t) * d) > dnode) s += t;
+  } while (t > 1);
+  const int gamma = i + s * d + (d < 0 ? d : 0);
+  const int lo = i < j ? i : j, hi = i < j ? j : i;
+  const int lc = (lo == gamma) ? (n - 1) + gamma : gamma;
+  const int rc = (hi == gamma + 1) ? (n - 1) + gamma + 1 : gamma + 1;
+  a.left[i] = lc;
+  a.right[i] = rc;
+  a.first[i] = (uint32_t)lo;
+  a.parent[lc] = i;
+  a.parent[rc] = i;
+  if (i == 0) a.parent[0] = -1;
+}
+
+// bottom-up box fit starting from leaf j (sorted position); second arrival continues
+RT_HD void refit_from_leaf(const BuildArrays& a, uint32_t j) {
+  const int n = (int)a.ntri;
+  const uint32_t t = a.vals[j];
+  const int leaf = (n - 1) + (int)j;
+  float4 lo = a.tri_lo[t], hi = a.tri_hi[t];
+  lo.w = u2f(1u);
+  a.node_lo[leaf] = lo;
+  a.node_hi[leaf] = hi;
+  if (n == 1) return;
+  int node = a.parent[leaf];
+  while (true) {
+    RT_FENCE();
+    if (RT_ATOMIC_ADD(&a.flags[node], 1u) == 0u) return;
+    const int lc = a.left[node], rc = a.right[node];
+    const float4 l0 = RT_LDCG(&a.node_lo[lc]), l1 = RT_LDCG(&a.node_hi[lc]);
+    const float4 r0 = RT_LDCG(&a.node_lo[rc]), r1 = RT_LDCG(&a.node_hi[rc]);
+    float4 nlo = make_float4(fminf(l0.x, r0.x), fminf(l0.y, r0.y), fminf(l0.z, r0.z), u2f(f2u(l0.w) + f2u(r0.w)));
+    float4 nhi = make_float4(fmaxf(l1.x, r1.x), fmaxf(l1.y, r1.y), fmaxf(l1.z, r1.z), 0.0f);
+    a.node_lo[node] = nlo;
+    a.node_hi[node] = nhi;
+    if (node == 0) return;
+    node = a.parent[node];
+  }
+}
+
+RT_HD float half_area(float4 lo, float4 hi) {
+  const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+  return dx * dy + dy * dz + dz * dx;
+}
+
+static const uint32_t WIDE_LEAF_MAX = 3;   // triangles per leaf child (unary count in 3 bits)
+
+// biased exponent e such that extent / 2^(e-127) <= 255
+RT_HD uint32_t quant_exponent(float extent) {
+  if (!(extent > 0.0f)) return 1u;
+  const float q = extent / 255.0f;
+  uint32_t b = f2u(q);
+  uint32_t e = (b >> 23) & 0xFFu;
+  if ((b & 0x7FFFFFu) != 0u) e += 1u;      // ceil(log2)
+  if (e < 1u) e = 1u;
+  // guard against rounding in the division: make sure ceil(extent * 2^-(e-127)) <= 255
+  while (e < 254u && ceilf(extent / u2f(e << 23)) > 255.0f) e++;
+  return e;
+}
+
+// Build wide node `w` from binary node work[w]: open the largest-area openable child
+// until there are 8, order children into octant slots, quantise, emit leaf triangles,
+// and queue the inner children as the next wide nodes.
+RT_HD void collapse_node(const BuildArrays& a, uint32_t w) {
+  const int n = (int)a.ntri;
+  const int root = (int)a.work[w];
+  int ch[8];
+  int nch = 0;
+  const float4 blo = a.node_lo[root], bhi = a.node_hi[root];
+  const bool root_is_leaf = root >= n - 1 || f2u(blo.w) <= WIDE_LEAF_MAX;
+  if (root_is_leaf) {
+    ch[nch++] = root;
+  } else {
+    ch[nch++] = a.left[root];
+    ch[nch++] = a.right[root];
+    while (nch < 8) {
+      int best = -1;
+      float barea = -1.0f;
+      for (int c = 0; c < nch; c++) {
+        const int id = ch[c];
+        if (id >= n - 1) continue;
+        const float4 lo = a.node_lo[id];
+        if (f2u(lo.w) <= WIDE_LEAF_MAX) continue;
+        const float ar = half_area(lo, a.node_hi[id]);
+        if (ar > barea) { barea = ar; best = c; }
+      }
+      if (best < 0) break;
+      const int id = ch[best];
+      ch[best] = a.left[id];
+      ch[nch++] = a.right[id];
+    }
+  }
+  // octant slot assignment: greedily take the (child, slot) pair with the largest
+  // projection of the child's centre offset on the slot's diagonal
+  const float cx = 0.5f * (blo.x + bhi.x), cy = 0.5f * (blo.y + bhi.y), cz = 0.5f * (blo.z + bhi.z);
+  float cost[8][8];
+  for (int c = 0; c < nch; c++) {
+    const float4 lo = a.node_lo[ch[c]], hi = a.node_hi[ch[c]];
+    const float ox = 0.5f * (lo.x + hi.x) - cx, oy = 0.5f * (lo.y + hi.y) - cy, oz = 0.5f * (lo.z + hi.z) - cz;
+    for (int s = 0; s < 8; s++)
+      cost[c][s] = ((s & 4) ? ox : -ox) + ((s & 2) ? oy : -oy) + ((s & 1) ? oz : -oz);
+  }
+  int slot_child[8];
+  for (int s = 0; s < 8; s++) slot_child[s] = -1;
+  uint32_t child_done = 0;
+  for (int it = 0; it < nch; it++) {
+    int bc = -1, bs = -1;
+    float bv = -3.0e38f;
+    for (int c = 0; c < nch; c++) {
+      if (child_done & (1u << c)) continue;
+      for (int s = 0; s < 8; s++) {
+        if (slot_child[s] >= 0) continue;
+        if (cost[c][s] > bv) { bv = cost[c][s]; bc = c; bs = s; }
+      }
+    }
+    slot_child[bs] = ch[bc];
+    child_done |= 1u << bc;
+  }
+  // classify, allocate
+  uint32_t imask = 0, n_inner = 0, n_tris = 0;
+  uint32_t cnt[8];
+  for (int s = 0; s < 8; s++) {
+    cnt[s] = 0;
+    const int id = slot_child[s];
+    if (id < 0) continue;
+    const uint32_t c = id >= n - 1 ? 1u : f2u(a.node_lo[id].w);
+    if (c <= WIDE_LEAF_MAX) { cnt[s] = c; n_tris += c; }
+    else { imask |= 1u << s; n_inner++; }
+  }
+  const uint32_t child_base = n_inner ? RT_ATOMIC_ADD(&a.counters[0], n_inner) : 0u;
+  const uint32_t tri_base = n_tris ? RT_ATOMIC_ADD(&a.counters[1], n_tris) : 0u;
+  // quantisation frame
+  const uint32_t ex = quant_exponent(bhi.x - blo.x), ey = quant_exponent(bhi.y - blo.y), ez = quant_exponent(bhi.z - blo.z);
+  const float isx = 1.0f / u2f(ex << 23), isy = 1.0f / u2f(ey << 23), isz = 1.0f / u2f(ez << 23);
+  uint32_t meta[2] = {0, 0}, qlx[2] = {0, 0}, qly[2] = {0, 0}, qlz[2] = {0, 0}, qhx[2] = {0, 0}, qhy[2] = {0, 0}, qhz[2] = {0, 0};
+  uint32_t inner_rank = 0, tri_off = 0;
+  for (int s = 0; s < 8; s++) {
+    const int id = slot_child[s];
+    const int wi = s >> 2, sh = 8 * (s & 3);
+    if (id < 0) {  // empty slot: inverted box, meta 0
+      qlx[wi] |= 0xFFu << sh; qly[wi] |= 0xFFu << sh; qlz[wi] |= 0xFFu << sh;
+      continue;
+    }
+    const float4 lo = a.node_lo[id], hi = a.node_hi[id];
+    float fl, fh;
+    fl = floorf((lo.x - blo.x) * isx); fh = ceilf((hi.x - blo.x) * isx);
+    qlx[wi] |= (uint32_t)fminf(fmaxf(fl, 0.0f), 255.0f) << sh; qhx[wi] |= (uint32_t)fminf(fmaxf(fh, 0.0f), 255.0f) << sh;
+    fl = floorf((lo.y - blo.y) * isy); fh = ceilf((hi.y - blo.y) * isy);
+    qly[wi] |= (uint32_t)fminf(fmaxf(fl, 0.0f), 255.0f) << sh; qhy[wi] |= (uint32_t)fminf(fmaxf(fh, 0.0f), 255.0f) << sh;
+    fl = floorf((lo.z - blo.z) * isz); fh = ceilf((hi.z - blo.z) * isz);
+    qlz[wi] |= (uint32_t)fminf(fmaxf(fl, 0.0f), 255.0f) << sh; qhz[wi] |= (uint32_t)fminf(fmaxf(fh, 0.0f), 255.0f) << sh;
+    if (imask & (1u << s)) {
+      meta[wi] |= (0x20u | (24u + (uint32_t)s)) << sh;
+      a.work[child_base + inner_rank] = (uint32_t)id;
+      inner_rank++;
+    } else {
+      const uint32_t c = cnt[s];
+      const uint32_t unary = c == 1 ? 1u : (c == 2 ? 3u : 7u);
+      meta[wi] |= ((unary << 5) | tri_off) << sh;
+      const uint32_t first = id >= n - 1 ? (uint32_t)(id - (n - 1)) : a.first[id];
+      for (uint32_t k = 0; k < c; k++) {
+        const uint32_t prim = a.vals[first + k];
+        const f3 p0 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)prim]));
+        const f3 p1 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)prim + 1]));
+        const f3 p2 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)prim + 2]));
+        float4* o = a.tris + 3 * (size_t)(tri_base + tri_off + k);
+        o[0] = make_float4(p0.x, p0.y, p0.z, u2f(prim));
+        o[1] = make_float4(p1.x, p1.y, p1.z, 0.0f);
+        o[2] = make_float4(p2.x, p2.y, p2.z, 0.0f);
+      }
+      tri_off += c;
+    }
+  }
+  uint4* o = a.wide + 5 * (size_t)w;
+  o[0] = make_uint4(f2u(blo.x), f2u(blo.y), f2u(blo.z), ex | (ey << 8) | (ez << 16) | (imask << 24));
+  o[1] = make_uint4(child_base, tri_base, meta[0], meta[1]);
+  o[2] = make_uint4(qlx[0], qlx[1], qly[0], qly[1]);
+  o[3] = make_uint4(qlz[0], qlz[1], qhx[0], qhx[1]);
+  o[4] = make_uint4(qhy[0], qhy[1], qhz[0], qhz[1]);
+}
+
+// Binary-tree cross-check layout (ACCEL_BVH2): node i -> 4 x float4, leaves = sorted slots
+RT_HD void emit_bvh2_node(const BuildArrays& a, int i, float4* out) {
+  const int n = (int)a.ntri;
+  const int lc = a.left[i], rc = a.right[i];
+  const float4 l0 = a.node_lo[lc], l1 = a.node_hi[lc], r0 = a.node_lo[rc], r1 = a.node_hi[rc];
+  const int c0 = lc >= n - 1 ? ~(lc - (n - 1)) : lc, c1 = rc >= n - 1 ? ~(rc - (n - 1)) : rc;
+  float4* o = out + 4 * (size_t)i;
+  o[0] = make_float4(l0.x, l0.y, l0.z, l1.x);
+  o[1] = make_float4(l1.y, l1.z, r0.x, r0.y);
+  o[2] = make_float4(r0.z, r1.x, r1.y, r1.z);
+  o[3] = make_float4(u2f((uint32_t)c0), u2f((uint32_t)c1), 0.0f, 0.0f);
+}
+
+// leaf triangle `slot` of the sorted (BVH2) or original (brute force) order
+RT_HD void emit_tri(const BuildArrays& a, uint32_t slot, uint32_t prim, float4* tris) {
+  const f3 p0 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)prim]));
+  const f3 p1 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)prim + 1]));
+  const f3 p2 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)prim + 2]));
+  float4* o = tris + 3 * (size_t)slot;
+  o[0] = make_float4(p0.x, p0.y, p0.z, u2f(prim));
+  o[1] = make_float4(p1.x, p1.y, p1.z, 0.0f);
+  o[2] = make_float4(p2.x, p2.y, p2.z, 0.0f);
+}
+
+}  // namespace rt

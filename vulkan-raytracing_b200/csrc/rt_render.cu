@@ -1,0 +1,544 @@
+// rt_render.cu — the wavefront frame pipeline for sm_100a: what one
+// vkCmdTraceRaysKHR(width,height,1) (main.cpp:2620-2624) does in the reference.
+//
+//   k_raygen                 shader.rgen:61-81  primary rays -> ray queue
+//   per bounce j = 0..maxBounceCount (shader.rgen:84):
+//     k_trace                traceRayEXT closest hit (shader.rgen:86-87): persistent warps
+//                            pull 32 rays at a time, traverse with a short stack in shared
+//                            memory, then ballot-compact the ray ids into the miss /
+//                            diffuse / specular queues (material-sorted)
+//     k_shade_miss           shader.rmiss + skybox lookup (shader.rgen:90-94)
+//     k_shade_diffuse        shader.rchit + back-face test, emits shadow rays (:97-110)
+//     k_shadow               traceRayEXT terminate-on-first-hit + Phong (:111-130)
+//     k_shade_spec           shader.rchit + mirror / refraction (:132-165) -> next queue
+//   k_resolve                color /= samples; imageStore (:183-185)
+//
+// Ray state in HBM between stages: 2 x float4 per ray (origin|sample slot, direction),
+// one uint4 hit record, 4-byte queue entries.  Each sample owns one float4 radiance slot
+// written exactly once, so the resolve sums samples in shader order and the image is
+// bit-reproducible whatever order warps retire in.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+
+#include "rt_internal.h"
+
+namespace rt {
+
+enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_STRIDE = 16 };
+constexpr int TRACE_THREADS = 128;
+constexpr int STACK_SM = 8;      // stack entries per thread kept in shared memory
+constexpr int STACK_LOCAL = 56;  // overflow entries in local memory
+
+// Traversal stack: the first STACK_SM entries live in shared memory (column per thread,
+// bank-conflict free), the rarely used rest in local memory.
+struct HybridStack {
+  uint2* sm;      // &smem[threadIdx.x], stride blockDim.x
+  uint2 loc[STACK_LOCAL];
+  int sp;
+  __device__ __forceinline__ void reset() { sp = 0; }
+  __device__ __forceinline__ bool empty() const { return sp == 0; }
+  __device__ __forceinline__ void push(uint2 v) {
+    if (sp < STACK_SM) sm[sp * TRACE_THREADS] = v;
+    else if (sp < STACK_SM + STACK_LOCAL) loc[sp - STACK_SM] = v;
+    sp++;
+  }
+  __device__ __forceinline__ uint2 pop() {
+    --sp;
+    return sp < STACK_SM ? sm[sp * TRACE_THREADS] : loc[sp - STACK_SM];
+  }
+};
+
+template <int ACCEL, bool ANY, bool COUNT>
+__device__ __forceinline__ bool trace_scene_t(const SceneDev& s, f3 o, f3 d, float tmin, float tmax, HitRec& best,
+                                              HybridStack& st, TravCounters* cnt) {
+  SceneDev sc = s;
+  sc.accel = ACCEL;  // compile-time constant: the untaken traversal variants fold away
+  return trace_scene<HybridStack, ANY, COUNT>(sc, o, d, tmin, tmax, best, st, cnt);
+}
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+
+// warp-aggregated append: returns the destination index for lanes with pred, ~0u otherwise
+__device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t* counter) {
+  const uint32_t mask = __ballot_sync(0xFFFFFFFFu, pred);
+  if (mask == 0u) return 0xFFFFFFFFu;
+  const int leader = __ffs(mask) - 1;
+  uint32_t base = 0;
+  if ((int)lane_id() == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+  base = __shfl_sync(0xFFFFFFFFu, base, leader);
+  return pred ? base + __popc(mask & ((1u << lane_id()) - 1u)) : 0xFFFFFFFFu;
+}
+
+// ---- ray generation ---------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_raygen(FrameUniforms U, uint32_t nslots, float4* __restrict__ rayO,
+                                                float4* __restrict__ rayD, float4* __restrict__ sample,
+                                                uint32_t* __restrict__ cnt) {
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const f3 amb = ambient_color();
+  for (uint64_t base = (uint64_t)w * 32; base < nslots; base += (uint64_t)warps * 32) {
+    const uint32_t s = (uint32_t)base + lane_id();
+    bool valid = false;
+    f3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
+    if (s < nslots) {
+      uint32_t x, y;
+      valid = slot_to_pixel(U, s / U.spp, x, y);
+      // every sample starts as tmpColor = Iamb*ka (shader.rgen:81); padding stays 0
+      sample[s] = valid ? make_float4(amb.x, amb.y, amb.z, 1.0f) : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (valid) raygen(U, x, y, s % U.spp, o, d);
+    }
+    const uint32_t dst = warp_append(valid, &cnt[C_NRAY]);
+    if (valid) {
+      rayO[dst] = make_float4(o.x, o.y, o.z, __uint_as_float(s));
+      rayD[dst] = make_float4(d.x, d.y, d.z, 0.0f);
+    }
+  }
+}
+
+// ---- closest-hit traversal ----------------------------------------------------------------
+template <int ACCEL, bool COUNT>
+__global__ void __launch_bounds__(TRACE_THREADS)
+    k_trace(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ rayO,
+            const float4* __restrict__ rayD, uint4* __restrict__ hits, uint32_t* __restrict__ qMiss,
+            uint32_t* __restrict__ qDiff, uint32_t* __restrict__ qSpec, rt_hit* __restrict__ primary,
+            unsigned long long* __restrict__ stats64) {
+  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  HybridStack st;
+  st.sm = &stack_sm[threadIdx.x];
+  TravCounters tc{0ull, 0ull};
+  const uint32_t n = cnt[C_NRAY];
+  while (true) {
+    uint32_t base = 0;
+    if (lane_id() == 0) base = atomicAdd(&cnt[C_WTRACE], 32u);
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (base >= n) break;
+    const uint32_t idx = base + lane_id();
+    const bool active = idx < n;
+    int kind = -1;  // 0 miss, 1 diffuse, 2 specular/other
+    if (active) {
+      const float4 ro = rayO[idx], rd = rayD[idx];
+      HitRec h;
+      const bool hit = trace_scene_t<ACCEL, false, COUNT>(scene, mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z), 0.001f,
+                                                          10000.0f, h, st, &tc);
+      hits[idx] = make_uint4(h.inst, h.prim, __float_as_uint(h.u), __float_as_uint(h.v));
+      kind = !hit ? 0 : (scene.inst[h.inst].type == 0u ? 1 : 2);
+      if (primary) {
+        const uint32_t s = __float_as_uint(ro.w);
+        uint32_t x, y;
+        slot_to_pixel(U, s / U.spp, x, y);
+        rt_hit out;
+        out.instance = h.inst; out.primitive = h.prim; out.t = hit ? h.t : 0.0f; out.u = h.u; out.v = h.v;
+        primary[((size_t)y * U.width + x) * U.spp + (s % U.spp)] = out;
+      }
+    }
+    uint32_t dst = warp_append(kind == 0, &cnt[C_NMISS]);
+    if (kind == 0) qMiss[dst] = idx;
+    dst = warp_append(kind == 1, &cnt[C_NDIFF]);
+    if (kind == 1) qDiff[dst] = idx;
+    dst = warp_append(kind == 2, &cnt[C_NSPEC]);
+    if (kind == 2) qSpec[dst] = idx;
+  }
+  if (COUNT) {
+    atomicAdd(&stats64[0], tc.nodes);
+    atomicAdd(&stats64[1], tc.tris);
+  }
+}
+
+// ---- miss: skybox -------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_shade_miss(SceneDev scene, const uint32_t* __restrict__ cnt,
+                                                    const uint32_t* __restrict__ qMiss, const float4* __restrict__ rayO,
+                                                    const float4* __restrict__ rayD, float4* __restrict__ sample) {
+  const uint32_t n = cnt[C_NMISS];
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t idx = qMiss[i];
+    const float4 rd = rayD[idx];
+    const uint32_t s = __float_as_uint(rayO[idx].w);
+    const f3 c = sky_sample(scene, mk3(rd.x, rd.y, -rd.z));  // shader.rgen:92
+    sample[s] = make_float4(c.x, c.y, c.z, 1.0f);
+  }
+}
+
+// ---- diffuse hits: back-face test, shadow-ray emission --------------------------------------
+__global__ void __launch_bounds__(256)
+    k_shade_diffuse(SceneDev scene, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ qDiff,
+                    const float4* __restrict__ rayO, const float4* __restrict__ rayD, const uint4* __restrict__ hits,
+                    float4* __restrict__ shadowQ) {
+  const uint32_t n = cnt[C_NDIFF];
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  for (uint64_t base = (uint64_t)w * 32; base < n; base += (uint64_t)warps * 32) {
+    const uint32_t i = (uint32_t)base + lane_id();
+    bool emit = false;
+    f3 P = mk3(0, 0, 0), N = mk3(0, 0, 0), d = mk3(0, 0, 0);
+    uint32_t s = 0;
+    if (i < n) {
+      const uint32_t idx = qDiff[i];
+      const uint4 h = hits[idx];
+      const float4 rd = rayD[idx];
+      s = __float_as_uint(rayO[idx].w);
+      d = mk3(rd.x, rd.y, rd.z);
+      rchit(scene, h.x, h.y, __uint_as_float(h.z), __uint_as_float(h.w), P, N);
+      emit = !(dot3(d, N) >= 0.0f);  // shader.rgen:104-105: back face keeps the ambient colour
+    }
+    const uint32_t dst = warp_append(emit, &cnt[C_NSHADOW]);
+    if (emit) {
+      shadowQ[3 * (size_t)dst + 0] = make_float4(P.x, P.y, P.z, __uint_as_float(s));
+      shadowQ[3 * (size_t)dst + 1] = make_float4(N.x, N.y, N.z, 0.0f);
+      shadowQ[3 * (size_t)dst + 2] = make_float4(d.x, d.y, d.z, 0.0f);
+    }
+  }
+}
+
+// ---- shadow rays + Phong ----------------------------------------------------------------------
+template <int ACCEL, bool COUNT>
+__global__ void __launch_bounds__(TRACE_THREADS)
+    k_shadow(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
+             float4* __restrict__ sample, unsigned long long* __restrict__ stats64) {
+  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  HybridStack st;
+  st.sm = &stack_sm[threadIdx.x];
+  TravCounters tc{0ull, 0ull};
+  const uint32_t n = cnt[C_NSHADOW];
+  while (true) {
+    uint32_t base = 0;
+    if (lane_id() == 0) base = atomicAdd(&cnt[C_WSHADOW], 32u);
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (base >= n) break;
+    const uint32_t i = base + lane_id();
+    if (i < n) {
+      const float4 q0 = shadowQ[3 * (size_t)i], q1 = shadowQ[3 * (size_t)i + 1], q2 = shadowQ[3 * (size_t)i + 2];
+      const f3 P = mk3(q0.x, q0.y, q0.z), N = mk3(q1.x, q1.y, q1.z), d = mk3(q2.x, q2.y, q2.z);
+      const uint32_t s = __float_as_uint(q0.w);
+      f3 so, L;
+      float dist;
+      shadow_ray(U, P, N, so, L, dist);
+      HitRec h;
+      const bool occluded = trace_scene_t<ACCEL, true, COUNT>(scene, so, L, 0.001f, dist, h, st, &tc);
+      if (!occluded) {
+        const f3 c = phong(U, d, N, L, s % U.spp);
+        sample[s] = make_float4(c.x, c.y, c.z, 1.0f);
+      }
+    }
+  }
+  if (COUNT) {
+    atomicAdd(&stats64[2], tc.nodes);
+    atomicAdd(&stats64[3], tc.tris);
+  }
+}
+
+// ---- mirror / refraction: next bounce ----------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    k_shade_spec(SceneDev scene, const uint32_t* __restrict__ cnt, uint32_t* __restrict__ cntNext,
+                 const uint32_t* __restrict__ qSpec, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
+                 const uint4* __restrict__ hits, float4* __restrict__ nextO, float4* __restrict__ nextD) {
+  const uint32_t n = cnt[C_NSPEC];
+  const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  for (uint64_t base = (uint64_t)w * 32; base < n; base += (uint64_t)warps * 32) {
+    const uint32_t i = (uint32_t)base + lane_id();
+    const bool active = i < n;
+    f3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
+    float slot = 0.0f;
+    if (active) {
+      const uint32_t idx = qSpec[i];
+      const uint4 h = hits[idx];
+      const float4 ro = rayO[idx], rd = rayD[idx];
+      slot = ro.w;
+      o = mk3(ro.x, ro.y, ro.z);
+      d = mk3(rd.x, rd.y, rd.z);
+      f3 P, N;
+      rchit(scene, h.x, h.y, __uint_as_float(h.z), __uint_as_float(h.w), P, N);
+      scatter(scene.inst[h.x].type, P, N, o, d);
+    }
+    const uint32_t dst = warp_append(active, &cntNext[C_NRAY]);
+    if (active) {
+      nextO[dst] = make_float4(o.x, o.y, o.z, slot);
+      nextD[dst] = make_float4(d.x, d.y, d.z, 0.0f);
+    }
+  }
+}
+
+// ---- resolve: color /= samples; imageStore ---------------------------------------------------
+__global__ void __launch_bounds__(256) k_resolve(FrameUniforms U, uint32_t npix, const float4* __restrict__ sample,
+                                                 void* __restrict__ out, uint32_t format) {
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x) {
+    uint32_t x, y;
+    const bool valid = slot_to_pixel(U, p, x, y);
+    float c[4] = {0.f, 0.f, 0.f, 0.f};
+    if (valid) {
+      for (uint32_t i = 0; i < U.spp; i++) {
+        const float4 s = sample[(size_t)p * U.spp + i];
+        c[0] += s.x; c[1] += s.y; c[2] += s.z; c[3] += 1.0f;   // color += vec4(tmpColor, 1)
+      }
+      const float fs = (float)U.spp;
+      c[0] = c[0] / fs; c[1] = c[1] / fs; c[2] = c[2] / fs; c[3] = c[3] / fs;
+    }
+    size_t dst;
+    if (U.shard_count <= 1) {
+      if (!valid) continue;
+      dst = (size_t)y * U.width + x;
+    } else {  // compact shard layout: tile after tile, each tile row-major
+      const uint32_t tile_px = U.tile_w * U.tile_h;
+      const uint32_t lt = p / tile_px;
+      const uint32_t tile = lt * U.shard_count + U.shard_index;
+      const uint32_t tx = x - (tile % U.tiles_x) * U.tile_w, ty = y - (tile / U.tiles_x) * U.tile_h;
+      dst = (size_t)lt * tile_px + (size_t)ty * U.tile_w + tx;
+    }
+    if (format == RT_FORMAT_RGBA8) {
+      ((uint32_t*)out)[dst] = to_unorm8(c[0]) | (to_unorm8(c[1]) << 8) | (to_unorm8(c[2]) << 16) | (to_unorm8(c[3]) << 24);
+    } else {
+      ((float4*)out)[dst] = make_float4(c[0], c[1], c[2], c[3]);
+    }
+  }
+}
+
+// gathered shard buffers -> row-major frame
+__global__ void __launch_bounds__(256) k_assemble(FrameUniforms U, uint32_t format, const void* __restrict__ gathered,
+                                                  void* __restrict__ frame, uint32_t shard_pixels) {
+  const uint32_t npix = U.width * U.height;
+  const uint32_t tile_px = U.tile_w * U.tile_h;
+  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x) {
+    const uint32_t x = p % U.width, y = p / U.width;
+    const uint32_t tile = (y / U.tile_h) * U.tiles_x + (x / U.tile_w);
+    const uint32_t shard = tile % U.shard_count, lt = tile / U.shard_count;
+    const size_t src = (size_t)shard * shard_pixels + (size_t)lt * tile_px + (size_t)(y % U.tile_h) * U.tile_w + (x % U.tile_w);
+    if (format == RT_FORMAT_RGBA8) ((uint32_t*)frame)[p] = ((const uint32_t*)gathered)[src];
+    else ((float4*)frame)[p] = ((const float4*)gathered)[src];
+  }
+}
+
+// ---- arbitrary ray batches (rt_trace_rays) ------------------------------------------------------
+template <int ACCEL, bool ANY, bool COUNT>
+__global__ void __launch_bounds__(TRACE_THREADS)
+    k_trace_batch(SceneDev scene, uint64_t n, const float* __restrict__ o, const float* __restrict__ d, float tmin,
+                  float tmax, rt_hit* __restrict__ out, unsigned long long* __restrict__ stats64) {
+  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  HybridStack st;
+  st.sm = &stack_sm[threadIdx.x];
+  TravCounters tc{0ull, 0ull};
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    HitRec h;
+    const bool hit = trace_scene_t<ACCEL, ANY, COUNT>(scene, mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]),
+                                                      mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]), tmin, tmax, h, st, &tc);
+    rt_hit r;
+    if (ANY) { r.instance = hit ? 0u : RT_MISS; r.primitive = RT_MISS; r.t = 0.f; r.u = 0.f; r.v = 0.f; }
+    else { r.instance = h.inst; r.primitive = h.prim; r.t = hit ? h.t : 0.0f; r.u = h.u; r.v = h.v; }
+    out[i] = r;
+  }
+  if (COUNT) {
+    atomicAdd(&stats64[0], tc.nodes);
+    atomicAdd(&stats64[1], tc.tris);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+struct FramePipeline {
+  size_t cap = 0;  // ray slots the buffers hold
+  float4 *rayO[2] = {nullptr, nullptr}, *rayD[2] = {nullptr, nullptr};
+  uint4* hits = nullptr;
+  uint32_t *qMiss = nullptr, *qDiff = nullptr, *qSpec = nullptr;
+  float4* shadowQ = nullptr;
+  float4* sample = nullptr;
+  uint32_t* cnt = nullptr;
+  size_t cnt_blocks = 0;
+  unsigned long long* stats64 = nullptr;
+  std::vector<uint32_t> h_cnt;
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  int trace_blocks[3][2] = {{0, 0}, {0, 0}, {0, 0}}, shadow_blocks[3][2] = {{0, 0}, {0, 0}, {0, 0}};
+};
+
+FramePipeline* pipeline_create() { return new FramePipeline(); }
+
+static void pipeline_free_buffers(FramePipeline* p) {
+  for (int i = 0; i < 2; i++) { cudaFree(p->rayO[i]); cudaFree(p->rayD[i]); p->rayO[i] = p->rayD[i] = nullptr; }
+  cudaFree(p->hits); cudaFree(p->qMiss); cudaFree(p->qDiff); cudaFree(p->qSpec); cudaFree(p->shadowQ); cudaFree(p->sample);
+  p->hits = nullptr; p->qMiss = p->qDiff = p->qSpec = nullptr; p->shadowQ = nullptr; p->sample = nullptr;
+  p->cap = 0;
+}
+
+void pipeline_destroy(FramePipeline* p) {
+  if (!p) return;
+  pipeline_free_buffers(p);
+  cudaFree(p->cnt); cudaFree(p->stats64);
+  for (auto& e : p->ev) if (e) cudaEventDestroy(e);
+  delete p;
+}
+
+static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std::string& err) {
+  if (slots > p->cap) {
+    pipeline_free_buffers(p);
+    for (int i = 0; i < 2; i++) {
+      RT_CUDA_TRY(cudaMalloc(&p->rayO[i], slots * sizeof(float4)), err);
+      RT_CUDA_TRY(cudaMalloc(&p->rayD[i], slots * sizeof(float4)), err);
+    }
+    RT_CUDA_TRY(cudaMalloc(&p->hits, slots * sizeof(uint4)), err);
+    RT_CUDA_TRY(cudaMalloc(&p->qMiss, slots * sizeof(uint32_t)), err);
+    RT_CUDA_TRY(cudaMalloc(&p->qDiff, slots * sizeof(uint32_t)), err);
+    RT_CUDA_TRY(cudaMalloc(&p->qSpec, slots * sizeof(uint32_t)), err);
+    RT_CUDA_TRY(cudaMalloc(&p->shadowQ, slots * 3 * sizeof(float4)), err);
+    RT_CUDA_TRY(cudaMalloc(&p->sample, slots * sizeof(float4)), err);
+    p->cap = slots;
+  }
+  if (bounces + 2 > p->cnt_blocks) {
+    cudaFree(p->cnt);
+    p->cnt = nullptr;
+    p->cnt_blocks = bounces + 2;
+    RT_CUDA_TRY(cudaMalloc(&p->cnt, p->cnt_blocks * C_STRIDE * sizeof(uint32_t)), err);
+  }
+  if (!p->stats64) RT_CUDA_TRY(cudaMalloc(&p->stats64, 8 * sizeof(unsigned long long)), err);
+  if (!p->ev[0]) {
+    RT_CUDA_TRY(cudaEventCreate(&p->ev[0]), err);
+    RT_CUDA_TRY(cudaEventCreate(&p->ev[1]), err);
+  }
+  return RT_OK;
+}
+
+template <class K>
+static int persistent_blocks(K kernel, int threads) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  return per_sm * sm_count();
+}
+
+static int stride_blocks(uint64_t n, int threads) {
+  const uint64_t want = (n + threads - 1) / threads;
+  return (int)std::max<uint64_t>(1, std::min<uint64_t>(want, (uint64_t)sm_count() * 8));
+}
+
+#define RT_DISPATCH_ACCEL(accel, counting, CALL)                          \
+  do {                                                                    \
+    if ((accel) == ACCEL_WIDE) { if (counting) { CALL(ACCEL_WIDE, true); } else { CALL(ACCEL_WIDE, false); } }        \
+    else if ((accel) == ACCEL_BVH2) { if (counting) { CALL(ACCEL_BVH2, true); } else { CALL(ACCEL_BVH2, false); } }   \
+    else { if (counting) { CALL(ACCEL_BRUTE, true); } else { CALL(ACCEL_BRUTE, false); } }                            \
+  } while (0)
+
+int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, rt_stats* stats, std::string& err) {
+  const FrameUniforms& U = rq.U;
+  const uint64_t npix = (uint64_t)U.n_local_tiles * U.tile_w * U.tile_h;
+  const uint64_t nslots = npix * U.spp;
+  if (nslots == 0) return RT_OK;
+  if (nslots > 0xFFFFFF00ull) { err = "frame too large: ray slots exceed 32 bits"; return RT_ERR_UNSUPPORTED; }
+  int rc = pipeline_reserve(p, nslots, U.max_bounce, err);
+  if (rc != RT_OK) return rc;
+  const uint32_t accel = rq.scene.accel;
+  const bool counting = rq.counting;
+  uint64_t launches = 0;
+  RT_CUDA_TRY(cudaEventRecord(p->ev[0], st), err);
+  RT_CUDA_TRY(cudaMemsetAsync(p->cnt, 0, p->cnt_blocks * C_STRIDE * sizeof(uint32_t), st), err);
+  RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
+  k_raygen<<<stride_blocks(nslots, 256), 256, 0, st>>>(U, (uint32_t)nslots, p->rayO[0], p->rayD[0], p->sample, p->cnt);
+  launches++;
+  int cur = 0;
+  uint32_t last_bounce = 0;
+  for (uint32_t j = 0; j <= U.max_bounce; j++) {
+    uint32_t* cj = p->cnt + (size_t)j * C_STRIDE;
+    uint32_t* cn = p->cnt + (size_t)(j + 1) * C_STRIDE;
+    rt_hit* prim = (j == 0 && rq.want_primary) ? rq.d_primary : nullptr;
+#define CALL_TRACE(A, C)                                                                                            \
+  {                                                                                                                 \
+    static int blocks = 0;                                                                                          \
+    if (!blocks) blocks = persistent_blocks(k_trace<A, C>, TRACE_THREADS);                                          \
+    k_trace<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->rayO[cur], p->rayD[cur], p->hits, p->qMiss, \
+                                                    p->qDiff, p->qSpec, prim, p->stats64);                          \
+  }
+    RT_DISPATCH_ACCEL(accel, counting, CALL_TRACE);
+#undef CALL_TRACE
+    k_shade_miss<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qMiss, p->rayO[cur], p->rayD[cur], p->sample);
+    k_shade_diffuse<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qDiff, p->rayO[cur], p->rayD[cur], p->hits, p->shadowQ);
+#define CALL_SHADOW(A, C)                                                                                 \
+  {                                                                                                       \
+    static int blocks = 0;                                                                                \
+    if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
+    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64); \
+  }
+    RT_DISPATCH_ACCEL(accel, counting, CALL_SHADOW);
+#undef CALL_SHADOW
+    launches += 4;
+    last_bounce = j;
+    if (j < U.max_bounce) {
+      k_shade_spec<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, cn, p->qSpec, p->rayO[cur], p->rayD[cur], p->hits,
+                                                   p->rayO[cur ^ 1], p->rayD[cur ^ 1]);
+      launches++;
+      cur ^= 1;
+      // deep bounce limits (MAX_BOUNCE_COUNT 63): stop as soon as no ray survives
+      if (j >= 3) {
+        uint32_t alive = 0;
+        RT_CUDA_TRY(cudaMemcpyAsync(&alive, cn + C_NRAY, sizeof alive, cudaMemcpyDeviceToHost, st), err);
+        RT_CUDA_TRY(cudaStreamSynchronize(st), err);
+        if (alive == 0) break;
+      }
+    }
+  }
+  if (rq.d_out) {
+    k_resolve<<<stride_blocks(npix, 256), 256, 0, st>>>(U, (uint32_t)npix, p->sample, rq.d_out, rq.output_format);
+    launches++;
+  }
+  RT_CUDA_TRY(cudaEventRecord(p->ev[1], st), err);
+  RT_CUDA_TRY(cudaGetLastError(), err);
+  // counters -> stats (also the synchronisation point of the frame)
+  p->h_cnt.resize(p->cnt_blocks * C_STRIDE);
+  unsigned long long h64[8];
+  RT_CUDA_TRY(cudaMemcpyAsync(p->h_cnt.data(), p->cnt, p->h_cnt.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), err);
+  RT_CUDA_TRY(cudaMemcpyAsync(h64, p->stats64, sizeof h64, cudaMemcpyDeviceToHost, st), err);
+  RT_CUDA_TRY(cudaStreamSynchronize(st), err);
+  if (stats) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]);
+    stats->frame_ms = ms;
+    stats->rays_primary = p->h_cnt[C_NRAY];
+    stats->rays_secondary = stats->rays_shadow = stats->n_miss = stats->n_hit = 0;
+    for (uint32_t j = 0; j <= last_bounce; j++) {
+      const uint32_t* c = &p->h_cnt[(size_t)j * C_STRIDE];
+      if (j > 0) stats->rays_secondary += c[C_NRAY];
+      stats->rays_shadow += c[C_NSHADOW];
+      stats->n_miss += c[C_NMISS];
+      stats->n_hit += (uint64_t)c[C_NDIFF] + c[C_NSPEC];
+    }
+    stats->nodes_visited = h64[0] + h64[2];
+    stats->tris_tested = h64[1] + h64[3];
+    stats->kernel_launches = launches;
+    stats->ray_state_bytes = 2 * sizeof(float4) + sizeof(uint4) + sizeof(uint32_t);
+  }
+  return RT_OK;
+}
+
+int pipeline_trace_batch(FramePipeline* p, const SceneDev& scene, uint64_t n, const float* d_o, const float* d_d,
+                         float tmin, float tmax, bool any_hit, bool counting, rt_hit* d_out, cudaStream_t st,
+                         rt_stats* stats, std::string& err) {
+  if (n == 0) return RT_OK;
+  if (!p->stats64) RT_CUDA_TRY(cudaMalloc(&p->stats64, 8 * sizeof(unsigned long long)), err);
+  RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
+  const int blocks = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + TRACE_THREADS - 1) / TRACE_THREADS, (uint64_t)sm_count() * 8));
+#define CALL_BATCH(A, C)                                                                                             \
+  {                                                                                                                  \
+    if (any_hit) k_trace_batch<A, true, C><<<blocks, TRACE_THREADS, 0, st>>>(scene, n, d_o, d_d, tmin, tmax, d_out, p->stats64); \
+    else k_trace_batch<A, false, C><<<blocks, TRACE_THREADS, 0, st>>>(scene, n, d_o, d_d, tmin, tmax, d_out, p->stats64);        \
+  }
+  RT_DISPATCH_ACCEL(scene.accel, counting, CALL_BATCH);
+#undef CALL_BATCH
+  RT_CUDA_TRY(cudaGetLastError(), err);
+  unsigned long long h64[8];
+  RT_CUDA_TRY(cudaMemcpyAsync(h64, p->stats64, sizeof h64, cudaMemcpyDeviceToHost, st), err);
+  RT_CUDA_TRY(cudaStreamSynchronize(st), err);
+  if (stats) {
+    stats->nodes_visited = h64[0];
+    stats->tris_tested = h64[1];
+    stats->kernel_launches = 1;
+  }
+  return RT_OK;
+}
+
+int assemble_shards(const FrameUniforms& U, uint32_t format, const void* gathered, void* frame, cudaStream_t st,
+                    std::string& err) {
+  const uint32_t tiles = U.tiles_x * U.tiles_y;
+  const uint32_t per_shard_tiles = (tiles + U.shard_count - 1) / U.shard_count;
+  const uint32_t shard_pixels = per_shard_tiles * U.tile_w * U.tile_h;
+  k_assemble<<<stride_blocks((uint64_t)U.width * U.height, 256), 256, 0, st>>>(U, format, gathered, frame, shard_pixels);
+  RT_CUDA_TRY(cudaGetLastError(), err);
+  return RT_OK;
+}
+
+}  // namespace rt

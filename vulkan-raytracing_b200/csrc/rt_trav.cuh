@@ -1,0 +1,352 @@
+// rt_trav.cuh — ray/scene intersection: what traceRayEXT (shader.rgen:86-87 closest hit,
+// shader.rgen:107-112 terminate-on-first-hit) and the driver's acceleration-structure
+// traversal do in the reference.  Per-ray RT_HD functions; kernels wrap them.
+//
+//   * watertight ray/triangle test (Woop, Benthin, Wald 2013), both faces (instances
+//     are created with TRIANGLE_FACING_CULL_DISABLE, main.cpp:548; geometry opaque,
+//     main.cpp:330), interval tmin < t < tmax, (u,v) = weights of vertices 1 and 2
+//     (hitCoordinate of shader.rchit:66-67);
+//   * closest hit = smallest t, ties to the lowest (instance, primitive);
+//   * compressed 8-wide BVH traversal (80-byte nodes, Ylitie et al. 2017 layout),
+//     binary LBVH traversal and brute force as cross-checks.
+#pragma once
+#include "rt_hd.cuh"
+
+namespace rt {
+
+enum { ACCEL_WIDE = 0, ACCEL_BVH2 = 1, ACCEL_BRUTE = 2 };
+static const uint32_t RT_MISS = 0xFFFFFFFFu;
+
+struct BlasDev {
+  const float4* nodes;   // WIDE: 5 x 16 B per node; BVH2: 4 x 16 B per node
+  const float4* tris;    // 3 x 16 B per triangle in leaf order: (v0, prim bits) (v1,-) (v2,-)
+  const float* verts;    // caller's vertex buffer, stride 6 floats (main.cpp:1678-1683)
+  const uint32_t* idx;   // caller's index buffer, 3 per triangle
+  uint32_t ntri;
+  uint32_t nnodes;
+};
+
+struct InstDev {
+  float o2w[12];
+  float w2o[12];
+  float wlo[3];
+  uint32_t mesh;
+  float whi[3];
+  uint32_t type;
+};
+
+struct SceneDev {
+  const BlasDev* blas;
+  const InstDev* inst;
+  uint32_t n_inst;
+  uint32_t accel;
+  const uint8_t* sky;  // 6 x h x w x RGBA8
+  uint32_t sky_w, sky_h;
+};
+
+struct HitRec {
+  uint32_t inst, prim;
+  float t, u, v;
+};
+
+struct TravCounters {
+  unsigned long long nodes, tris;
+};
+
+// ---- object-space ray with the watertight shear constants -------------------------------
+struct RayObj {
+  f3 o, d;
+  int kx, ky, kz;
+  float Sx, Sy, Sz;
+  f3 idir;          // 1/d with |d| clamped away from 0 (box tests only)
+  uint32_t octinv4; // (dx>=0?4:0 | dy>=0?2:0 | dz>=0?1:0) replicated in 4 bytes
+};
+
+RT_HD float sel3(f3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+
+RT_HD float safe_rcp_dir(float d) {
+  float a = fabsf(d) > 1e-20f ? d : copysignf(1e-20f, d);
+  return 1.0f / a;
+}
+
+RT_HD RayObj ray_setup(f3 o, f3 d) {
+  RayObj r;
+  r.o = o;
+  r.d = d;
+  int kz = 0;
+  float m = fabsf(d.x);
+  if (fabsf(d.y) > m) { kz = 1; m = fabsf(d.y); }
+  if (fabsf(d.z) > m) { kz = 2; }
+  int kx = kz == 2 ? 0 : kz + 1;
+  int ky = kx == 2 ? 0 : kx + 1;
+  float dz = sel3(d, kz);
+  if (dz < 0.0f) { int t = kx; kx = ky; ky = t; }
+  r.kx = kx; r.ky = ky; r.kz = kz;
+  r.Sx = sel3(d, kx) / dz;
+  r.Sy = sel3(d, ky) / dz;
+  r.Sz = 1.0f / dz;
+  r.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
+  r.octinv4 = ((d.x >= 0.0f ? 4u : 0u) | (d.y >= 0.0f ? 2u : 0u) | (d.z >= 0.0f ? 1u : 0u)) * 0x01010101u;
+  return r;
+}
+
+// Returns true when tmin < t <= tlimit.  Same operation sequence as the oracle.
+RT_HD bool tri_test(const RayObj& r, f3 p0, f3 p1, f3 p2, float tmin, float tlimit, float& t, float& u, float& v) {
+  f3 A = sub3(p0, r.o), B = sub3(p1, r.o), C = sub3(p2, r.o);
+  float Akz = sel3(A, r.kz), Bkz = sel3(B, r.kz), Ckz = sel3(C, r.kz);
+  float Ax = fmaf(-r.Sx, Akz, sel3(A, r.kx)), Ay = fmaf(-r.Sy, Akz, sel3(A, r.ky));
+  float Bx = fmaf(-r.Sx, Bkz, sel3(B, r.kx)), By = fmaf(-r.Sy, Bkz, sel3(B, r.ky));
+  float Cx = fmaf(-r.Sx, Ckz, sel3(C, r.kx)), Cy = fmaf(-r.Sy, Ckz, sel3(C, r.ky));
+  // products and difference rounded separately: exactly antisymmetric edge functions
+  float U = Cx * By - Cy * Bx;
+  float V = Ax * Cy - Ay * Cx;
+  float W = Bx * Ay - By * Ax;
+  if (U == 0.0f || V == 0.0f || W == 0.0f) {
+    U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+    V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+    W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+  }
+  if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
+  float det = (U + V) + W;
+  if (det == 0.0f) return false;
+  float Az = r.Sz * Akz, Bz = r.Sz * Bkz, Cz = r.Sz * Ckz;
+  float T = fmaf(W, Cz, fmaf(V, Bz, U * Az));
+  float rdet = 1.0f / det;
+  float tt = T * rdet;
+  if (!(tt > tmin && tt <= tlimit)) return false;
+  t = tt;
+  u = V * rdet;
+  v = W * rdet;
+  return true;
+}
+
+// Running closest hit with the tie rule.
+RT_HD void consider_hit(HitRec& best, uint32_t inst, uint32_t prim, float t, float u, float v) {
+  if (t < best.t || (t == best.t && (inst < best.inst || (inst == best.inst && prim < best.prim)))) {
+    best.inst = inst; best.prim = prim; best.t = t; best.u = u; best.v = v;
+  }
+}
+
+// Leaf triangle from the packed leaf array (3 x float4).
+template <bool ANY, bool COUNT>
+RT_HD bool test_leaf_tri(const BlasDev& b, uint32_t slot, const RayObj& r, float tmin, uint32_t inst, HitRec& best,
+                         TravCounters* cnt) {
+  const float4 a = RT_LDG(&b.tris[3 * (size_t)slot + 0]);
+  const float4 bb = RT_LDG(&b.tris[3 * (size_t)slot + 1]);
+  const float4 c = RT_LDG(&b.tris[3 * (size_t)slot + 2]);
+  if (COUNT) cnt->tris++;
+  float t, u, v;
+  if (tri_test(r, mk3(a.x, a.y, a.z), mk3(bb.x, bb.y, bb.z), mk3(c.x, c.y, c.z), tmin, best.t, t, u, v)) {
+    if (ANY) { best.inst = inst; return true; }
+    consider_hit(best, inst, f2u(a.w), t, u, v);
+  }
+  return false;
+}
+
+// ---- brute force ------------------------------------------------------------------------
+template <bool ANY, bool COUNT>
+RT_HD bool trace_brute(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, TravCounters* cnt) {
+  for (uint32_t s = 0; s < b.ntri; s++)
+    if (test_leaf_tri<ANY, COUNT>(b, s, r, tmin, inst, best, cnt)) return true;
+  return false;
+}
+
+// conservative slab test against an explicit box, interval [tmin, tmax]
+RT_HD bool slab_test(const RayObj& r, float lox, float loy, float loz, float hix, float hiy, float hiz, float tmin,
+                     float tmax) {
+  float t1 = (lox - r.o.x) * r.idir.x, t2 = (hix - r.o.x) * r.idir.x;
+  float tn = fmaxf(tmin, fminf(t1, t2) * 0.99999f), tf = fminf(tmax, fmaxf(t1, t2) * 1.00001f);
+  t1 = (loy - r.o.y) * r.idir.y; t2 = (hiy - r.o.y) * r.idir.y;
+  tn = fmaxf(tn, fminf(t1, t2) * 0.99999f); tf = fminf(tf, fmaxf(t1, t2) * 1.00001f);
+  t1 = (loz - r.o.z) * r.idir.z; t2 = (hiz - r.o.z) * r.idir.z;
+  tn = fmaxf(tn, fminf(t1, t2) * 0.99999f); tf = fminf(tf, fmaxf(t1, t2) * 1.00001f);
+  return tn <= tf;
+}
+
+// ---- binary LBVH (cross-check path) -----------------------------------------------------
+// node = 4 x float4: (c0.lo.xyz, c0.hi.x) (c0.hi.yz, c1.lo.xy) (c1.lo.z, c1.hi.xyz)
+//                    (child0, child1, -, -) as int bits; child < 0: leaf, triangle slot ~child
+template <class Stack, bool ANY, bool COUNT>
+RT_HD bool trace_bvh2(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
+                      TravCounters* cnt) {
+  if (b.ntri == 0) return false;
+  if (b.ntri == 1) return test_leaf_tri<ANY, COUNT>(b, 0, r, tmin, inst, best, cnt);
+  st.reset();
+  int node = 0;
+  while (true) {
+    const float4 n0 = RT_LDG(&b.nodes[4 * (size_t)node + 0]);
+    const float4 n1 = RT_LDG(&b.nodes[4 * (size_t)node + 1]);
+    const float4 n2 = RT_LDG(&b.nodes[4 * (size_t)node + 2]);
+    const float4 n3 = RT_LDG(&b.nodes[4 * (size_t)node + 3]);
+    if (COUNT) cnt->nodes++;
+    bool h0 = slab_test(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t);
+    bool h1 = slab_test(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t);
+    int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
+    int next = -1;
+    bool have = false;
+    if (h0) {
+      if (c0 < 0) { if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~c0, r, tmin, inst, best, cnt)) return true; }
+      else { next = c0; have = true; }
+    }
+    if (h1) {
+      if (c1 < 0) { if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~c1, r, tmin, inst, best, cnt)) return true; }
+      else if (have) st.push(make_uint2((uint32_t)c1, 0u));
+      else { next = c1; have = true; }
+    }
+    if (have) { node = next; continue; }
+    if (st.empty()) break;
+    node = (int)st.pop().x;
+  }
+  return false;
+}
+
+// ---- compressed 8-wide BVH --------------------------------------------------------------
+// 80-byte node = 5 x 16 B:
+//   n0 = (p.x, p.y, p.z, ex | ey<<8 | ez<<16 | imask<<24)       quantisation frame + inner mask
+//   n1 = (child_base, tri_base, meta[0..3], meta[4..7])
+//   n2 = (qlo_x[0..3], qlo_x[4..7], qlo_y[0..3], qlo_y[4..7])
+//   n3 = (qlo_z[0..3], qlo_z[4..7], qhi_x[0..3], qhi_x[4..7])
+//   n4 = (qhi_y[0..3], qhi_y[4..7], qhi_z[0..3], qhi_z[4..7])
+// child box = p + q * 2^(e-127).  meta: inner child = 0x20 | (24 + slot); leaf child =
+// (unary triangle count 1/3/7) << 5 | first-triangle offset from tri_base; empty = 0.
+RT_HD uint32_t byte_perm_lo(uint32_t w, int i) {
+#if defined(__CUDA_ARCH__)
+  return __byte_perm(w, 0x4B000000u, 0x7650u | (uint32_t)i);
+#else
+  return 0x4B000000u | ((w >> (8 * i)) & 0xFFu);
+#endif
+}
+// byte i of w as an exact float, without an integer->float conversion
+RT_HD float byte2f(uint32_t w, int i) { return u2f(byte_perm_lo(w, i)) - 8388608.0f; }
+
+RT_HD uint32_t sign_extend_s8x4(uint32_t x) { return ((x & 0x80808080u) >> 7) * 0xFFu; }
+
+template <bool COUNT>
+RT_HD uint32_t wide_node_test(const float4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
+                              const RayObj& r, float tmin, float tmax) {
+  const uint32_t e = f2u(n0.w);
+  const float sx = u2f((e & 0xFFu) << 23), sy = u2f(((e >> 8) & 0xFFu) << 23), sz = u2f(((e >> 16) & 0xFFu) << 23);
+  // near planes shrink toward the origin, far planes grow: conservative against rounding
+  const float ax = sx * r.idir.x, ay = sy * r.idir.y, az = sz * r.idir.z;
+  const float bx = (n0.x - r.o.x) * r.idir.x, by = (n0.y - r.o.y) * r.idir.y, bz = (n0.z - r.o.z) * r.idir.z;
+  const float kn = 0.99999f, kf = 1.00001f;
+  const float anx = ax * kn, any_ = ay * kn, anz = az * kn, bnx = bx * kn, bny = by * kn, bnz = bz * kn;
+  const float afx = ax * kf, afy = ay * kf, afz = az * kf, bfx = bx * kf, bfy = by * kf, bfz = bz * kf;
+  const bool px = r.d.x >= 0.0f, py = r.d.y >= 0.0f, pz = r.d.z >= 0.0f;
+  uint32_t hitmask = 0;
+#pragma unroll
+  for (int half = 0; half < 2; half++) {
+    const uint32_t meta4 = half ? n1.w : n1.z;
+    const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+    const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+    const uint32_t bit_index4 = (meta4 ^ (r.octinv4 & inner_mask4)) & 0x1F1F1F1Fu;
+    const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+    const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
+    const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
+    const uint32_t nx = px ? qlox : qhix, fx = px ? qhix : qlox;
+    const uint32_t ny = py ? qloy : qhiy, fy = py ? qhiy : qloy;
+    const uint32_t nz = pz ? qloz : qhiz, fz = pz ? qhiz : qloz;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      float tnx = fmaf(byte2f(nx, j), anx, bnx), tny = fmaf(byte2f(ny, j), any_, bny), tnz = fmaf(byte2f(nz, j), anz, bnz);
+      float tfx = fmaf(byte2f(fx, j), afx, bfx), tfy = fmaf(byte2f(fy, j), afy, bfy), tfz = fmaf(byte2f(fz, j), afz, bfz);
+      float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+      float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
+      if (tn <= tf) {
+        uint32_t cb = (child_bits4 >> (8 * j)) & 0xFFu, bi = (bit_index4 >> (8 * j)) & 0xFFu;
+        hitmask |= cb << bi;
+      }
+    }
+  }
+  return hitmask;
+}
+
+template <class Stack, bool ANY, bool COUNT>
+RT_HD bool trace_wide(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
+                      TravCounters* cnt) {
+  if (b.ntri == 0) return false;
+  st.reset();
+  const uint4* nodes = (const uint4*)b.nodes;
+  uint2 ngroup = make_uint2(0u, 0x80000000u);
+  uint2 tgroup = make_uint2(0u, 0u);
+  while (true) {
+    if (ngroup.y > 0x00FFFFFFu) {
+      const uint32_t hits = ngroup.y;
+      const int child_bit = bfind32(hits);
+      const uint32_t child_base = ngroup.x;
+      ngroup.y &= ~(1u << child_bit);
+      if (ngroup.y > 0x00FFFFFFu) st.push(ngroup);
+      const uint32_t slot = (uint32_t)(child_bit - 24) ^ (r.octinv4 & 7u);
+      const uint32_t rel = (uint32_t)popc32(hits & ~(0xFFFFFFFFu << slot) & 0xFFu);
+      const size_t ni = 5 * (size_t)(child_base + rel);
+      const float4 n0 = RT_LDG(&b.nodes[ni]);
+      const uint4 n1 = RT_LDG(&nodes[ni + 1]);
+      const uint4 n2 = RT_LDG(&nodes[ni + 2]);
+      const uint4 n3 = RT_LDG(&nodes[ni + 3]);
+      const uint4 n4 = RT_LDG(&nodes[ni + 4]);
+      if (COUNT) cnt->nodes++;
+      const uint32_t hm = wide_node_test<COUNT>(n0, n1, n2, n3, n4, r, tmin, best.t);
+      ngroup.x = n1.x;
+      tgroup.x = n1.y;
+      ngroup.y = (hm & 0xFF000000u) | (f2u(n0.w) >> 24);
+      tgroup.y = hm & 0x00FFFFFFu;
+    } else {
+      tgroup = ngroup;
+      ngroup = make_uint2(0u, 0u);
+    }
+    while (tgroup.y != 0u) {
+      const int ti = bfind32(tgroup.y);
+      tgroup.y &= ~(1u << ti);
+      if (test_leaf_tri<ANY, COUNT>(b, tgroup.x + (uint32_t)ti, r, tmin, inst, best, cnt)) return true;
+    }
+    if (ngroup.y <= 0x00FFFFFFu) {
+      if (st.empty()) break;
+      ngroup = st.pop();
+    }
+  }
+  return false;
+}
+
+// ---- two-level trace over all instances ---------------------------------------------------
+// The ray is taken into each instance's object space (direction not renormalised, so t
+// is shared), as the Vulkan TLAS->BLAS traversal does.  Returns true when something was
+// hit; `best` then holds the closest hit (for ANY only best.inst is meaningful).
+template <class Stack, bool ANY, bool COUNT>
+RT_HD bool trace_scene(const SceneDev& s, f3 o, f3 d, float tmin, float tmax, HitRec& best, Stack& st,
+                       TravCounters* cnt) {
+  best.inst = RT_MISS;
+  best.prim = RT_MISS;
+  best.t = u2f(f2u(tmax) - 1u);  // nextafter(tmax, -inf): "t <= best.t" == "t < tmax"
+  best.u = 0.0f;
+  best.v = 0.0f;
+  for (uint32_t i = 0; i < s.n_inst; i++) {
+    const InstDev& in = s.inst[i];
+    if (s.n_inst > 1) {  // cull against the instance's padded world box
+      RayObj rw;
+      rw.o = o;
+      rw.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
+      if (!slab_test(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], tmin, best.t)) continue;
+    }
+    const RayObj r = ray_setup(xform_point(in.w2o, o), xform_vector(in.w2o, d));
+    const BlasDev& b = s.blas[in.mesh];
+    bool hit;
+    if (s.accel == ACCEL_WIDE) hit = trace_wide<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
+    else if (s.accel == ACCEL_BVH2) hit = trace_bvh2<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
+    else hit = trace_brute<ANY, COUNT>(b, r, tmin, i, best, cnt);
+    if (ANY && hit) return true;
+  }
+  return best.inst != RT_MISS;
+}
+
+// Simple array stack (emulation and overflow part of the GPU stack).
+template <int N>
+struct ArrayStack {
+  uint2 e[N];
+  int sp;
+  RT_HD void reset() { sp = 0; }
+  RT_HD bool empty() const { return sp == 0; }
+  RT_HD void push(uint2 v) { if (sp < N) e[sp++] = v; }
+  RT_HD uint2 pop() { return e[--sp]; }
+};
+
+}  // namespace rt

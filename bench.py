@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 ray-tracing core (contract in the task statement).
+
+A "step" is one frame of the hot path (rt_render_frame) on a synthetic scene:
+  N = 1   BASELINE config C3: refractive armadillo (stand-in mesh, 327 680 triangles) in the
+          orbiting slot + diffuse teapot in the centre slot, 3840x2160, 4 spp, depth 8.
+  N > 1   BASELINE config C4: the same scene at 7680x4320, tile-sharded over the N GPUs (scene
+          replicated, one process per GPU), per-GPU tiles gathered over NCCL and assembled on
+          rank 0.
+metric: Mrays/s = traceRayEXT-equivalents (closest-hit + shadow traces) issued per second,
+whole job.  `value` is timed with the frame left in HBM; `e2e` is the same metric through the
+C ABI with a HOST output buffer (uniforms H2D + frame D2H inside the timed region).
+
+`--impl reference` times the reference's CPU implementation of the path: the reference has no
+CPU ray tracer and cannot be built here, so this is the oracle port (oracle/liboracle.so) on
+all host cores, each step a bounded centred crop of the same frame.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import __graft_entry__ as graft  # noqa: E402
+
+WORKLOADS = {
+    # name: (scene builder name, width, height, depth, spp)
+    "c3": ("c3_scene", 3840, 2160, 8, 4),
+    "c4": ("c3_scene", 7680, 4320, 8, 4),
+    "c2": ("c2_scene", 1920, 1080, 4, 4),
+}
+WORKLOAD_TEXT = {
+    "c3": "C3 armadillo_standin(327680 tri, refractive, T(0,0,5)) + teapot(diffuse, shadow rays) 3840x2160 spp4 depth8",
+    "c4": "C4 armadillo_standin(327680 tri, refractive) + teapot(diffuse) 7680x4320 spp4 depth8, tile-sharded",
+    "c2": "C2 teapot(mirror) + teapot(refractive, T(0,0,5)) 1920x1080 spp4 depth4",
+}
+CPU_CROP_FRACTION = 3  # the CPU arm renders the centred (W/3 x H/3) crop of the frame
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sky", type=int, default=2048, help="procedural skybox face size")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu = [], None, str(gpu_index)
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", self.gpu], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for k, n in enumerate(names):
+                    if r[5 + k].lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def crop_of(w, h):
+    cw, ch = w // CPU_CROP_FRACTION, h // CPU_CROP_FRACTION
+    x0, y0 = (w - cw) // 2, (h - ch) // 2
+    return (x0, y0, x0 + cw, y0 + ch)
+
+
+def cpu_arm(rt, inputs, cam, params, steps, warmup):
+    """Oracle port on all host cores over the centred crop; returns (Mrays/s, ms/step, cores, sample)."""
+    import oracle_binding as ob
+    osc = ob.OracleScene(inputs)
+    crop = crop_of(params.width, params.height)
+    cores = ob.lib().orc_num_threads()
+    rays, times = 0, []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        r = osc.render(cam, params, crop=crop, want=("rgba8", "counts"))
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+            c = r["counts"]
+            rays = c["primary"] + c["secondary"] + c["shadow"]
+    total = sum(times)
+    sample = (f"centred {crop[2]-crop[0]}x{crop[3]-crop[1]} crop of the {params.width}x{params.height} frame, "
+              f"{rays} rays per step, oracle BVH mode, OpenMP over rows")
+    return rays * len(times) / total / 1e6, 1e3 * total / len(times), cores, sample
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix):
+    """Algorithmic work of the traversal kernels (k_trace + k_shadow) of one frame, DESIGN.md §5."""
+    n_node, n_tri = st_count["nodes_visited"], st_count["tris_tested"]
+    n_closest = st_count["rays_primary"] + st_count["rays_secondary"]
+    n_shadow = st_count["rays_shadow"]
+    node_b, tri_b = st_count["node_bytes"], st_count["tri_bytes"]
+    trav_bytes = n_node * node_b + n_tri * tri_b + n_closest * (32 + 16 + 4) + n_shadow * (48 + 16)
+    trav_flops = n_node * 8 * 24 + n_tri * 50
+    achieved = trav_bytes / (trav_ms * 1e-3) / 1e9
+    frame_bytes = (trav_bytes + st_count["n_hit"] * 84 + st_count["n_miss"] * 16 + n_closest * 32 + npix * 4)
+    frame_flops = trav_flops + st_count["n_hit"] * 120
+    t_roof = max(frame_bytes / (hbm_gbs * 1e9), frame_flops / (fp32_tflops * 1e12) if fp32_tflops else 0.0)
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    traffic = None
+    if os.path.exists(path):
+        try:
+            traffic = json.load(open(path)).get("k_trace_dram_bytes_per_frame")
+        except Exception:
+            traffic = None
+    return {
+        "bound": "hbm", "kernel": "k_trace+k_shadow (all traversal launches of one frame)",
+        "achieved": round(achieved, 1), "peak": hbm_gbs, "peak_source": hbm_src, "unit": "GB/s",
+        "frac": round(achieved / hbm_gbs, 4), "traffic": traffic,
+        "algorithmic_bytes_per_frame": int(trav_bytes), "traversal_ms": round(trav_ms, 4),
+        "nodes_visited": int(n_node), "tris_tested": int(n_tri), "node_bytes": node_b, "tri_bytes": tri_b,
+        "flop_term": {"flops_per_frame": int(trav_flops), "achieved_tflops": round(trav_flops / (trav_ms * 1e-3) / 1e12, 3),
+                      "fp32_peak_tflops_measured": round(fp32_tflops, 2),
+                      "frac": round(trav_flops / (trav_ms * 1e-3) / 1e12 / fp32_tflops, 4) if fp32_tflops else None},
+        "frame_roofline_frac": round(t_roof / (frame_ms * 1e-3), 4),
+    }
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    wl = args.workload or ("c3" if args.gpus <= 1 else "c4")
+    builder, W, H, depth, spp = WORKLOADS[wl]
+    config = {"workload": WORKLOAD_TEXT[wl], "width": W, "height": H, "spp": spp, "max_bounce_count": depth,
+              "skybox": f"procedural {args.sky}x{args.sky}x6 RGBA8", "mesh": "armadillo_standin" if wl != "c2" else "teapot",
+              "l2": "ray-state buffers (GBs per frame) exceed L2; a 512 MiB buffer is also overwritten between steps"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        graft.build() if not os.path.exists(os.path.join(ROOT, "oracle", "liboracle.so")) else None
+        rt = graft.load_package()
+        import scenes
+        inputs = getattr(scenes, builder)(rt, sky_size=args.sky)
+        params = rt.FrameParams.make(W, H, depth, spp)
+        v, ms, cores, sample = cpu_arm(rt, inputs, rt.CameraVectors.default(), params, args.steps, args.warmup)
+        print(json.dumps({
+            "impl": "reference", "metric": "Mrays/s", "value": round(v, 3), "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+            "cpu_baseline": {"value": round(v, 3), "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": round(v, 3), "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "the reference has no CPU ray tracer and its Vulkan path is unavailable on this box; "
+                    "this is the oracle port of its shaders on the host cores"}))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    rt = graft.load_package()
+    import scenes
+    if rt.device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device: the render path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+    inputs = getattr(scenes, builder)(rt, sky_size=args.sky)
+    scene = rt.Scene(inputs, device_id=local_rank)
+    build_ms = scene.stats()["build_ms"]
+    scene.set_stream(torch.cuda.current_stream().cuda_stream)
+    cam = rt.CameraVectors.default()
+    sharded = world > 1
+    p_dev = rt.FrameParams.make(W, H, depth, spp, output_location=rt.LOCATION_DEVICE,
+                                shard_index=rank if sharded else 0, shard_count=world if sharded else 1)
+    npix_local = int(rt.rt_lib().rt_frame_shard_pixels(C.byref(p_dev))) if sharded else W * H
+    local = torch.zeros((npix_local, 4), dtype=torch.uint8, device=dev)
+    gathered = torch.zeros((world, npix_local, 4), dtype=torch.uint8, device=dev) if (sharded and rank == 0) else None
+    frame = torch.zeros((H, W, 4), dtype=torch.uint8, device=dev) if rank == 0 else None
+    host = torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    launches = {"n": 0}
+
+    def step(to_host):
+        scene.render_into(cam, p_dev, local.data_ptr())
+        launches["n"] += scene.stats()["kernel_launches"]
+        if sharded:
+            dist.gather(local, [gathered[i] for i in range(world)] if rank == 0 else None, dst=0)
+            if rank == 0:
+                scene.assemble_shards(p_dev, gathered.data_ptr(), frame.data_ptr())
+                launches["n"] += 1
+        if to_host and rank == 0:
+            src = frame if sharded else local.view(H, W, 4)
+            host.copy_(src, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+    def timed(to_host, steps):
+        ms, rays = 0.0, 0
+        for _ in range(steps):
+            flush.zero_()
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            step(to_host)
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+            st = scene.stats()
+            r = torch.tensor([st["rays_primary"] + st["rays_secondary"] + st["rays_shadow"]], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dist.all_reduce(r, op=dist.ReduceOp.SUM)
+            ms += float(t.item())
+            rays += int(r.item())
+        return ms, rays
+
+    for _ in range(max(args.warmup, 3)):
+        step(False)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches["n"] = 0
+    ms_dev, rays_dev = timed(False, args.steps)
+    n_launch = launches["n"]
+    st_last = scene.stats()
+    ms_e2e, rays_e2e = timed(True, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # counting frame (outside the timed region): exact node / triangle-test counts
+    scene.set_counting(True)
+    scene.render_into(cam, p_dev, local.data_ptr())
+    st_count = scene.stats()
+    scene.set_counting(False)
+    fp32 = rt.measure_fp32_tflops(local_rank) if rank == 0 else 0.0
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
+    hbm, hbm_src = load_peaks()
+    value = rays_dev / (ms_dev * 1e-3) / 1e6
+    e2e_v = rays_e2e / (ms_e2e * 1e-3) / 1e6
+    out = {
+        "metric": "Mrays/s", "value": round(value, 2), "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(ms_dev / args.steps, 4), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+        "frame_ms": round(ms_dev / args.steps, 4), "rays_per_frame": rays_dev // args.steps, "build_ms": round(build_ms, 3),
+        "e2e": {"value": round(e2e_v, 2), "unit": "Mrays/s", "ms_per_step": round(ms_e2e / args.steps, 4),
+                "h2d_bytes_per_step": C.sizeof(rt.CameraVectors) + C.sizeof(rt.FrameParams), "d2h_bytes_per_step": W * H * 4},
+        "gpu_launches": int(n_launch), "clocks": clocks,
+        "stage_ms": {"trace": round(st_last["trace_ms"], 4), "shadow": round(st_last["shadow_ms"], 4),
+                     "shade_raygen_resolve": round(st_last["shade_ms"], 4), "frame_in_library": round(st_last["frame_ms"], 4)},
+        "bvh": {"nodes": st_last["bvh_nodes"], "bytes": st_last["bvh_bytes"]},
+    }
+    out["roofline"] = roofline(st_count, st_last["trace_ms"] + st_last["shadow_ms"], st_last["frame_ms"], hbm, hbm_src, fp32,
+                               npix_local)
+    if world == 1 and not args.no_cpu_baseline:
+        p_cpu = rt.FrameParams.make(W, H, depth, spp)
+        v, ms, cores, sample = cpu_arm(rt, inputs, cam, p_cpu, 1, 0)
+        out["cpu_baseline"] = {"value": round(v, 3), "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample,
+                               "ms_per_sample": round(ms, 1)}
+    print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -206,6 +206,10 @@ int rt_trace_rays(void* scene, uint64_t n, const float* origins, const float* di
                   float tmin, float tmax, int any_hit, rt_hit* hits_out);
 int rt_get_stats(void* scene, rt_stats* out);
 
+/* FP32 FMA throughput of the CUDA cores measured with a dependent-chain microbenchmark
+ * (TFLOP/s): the denominator of the FLOP term of the traversal roofline. */
+int rt_measure_fp32_tflops(int device_id, double* tflops_out);
+
 /* --- sorting primitive (exported for tests) ---------------------------------- */
 /* The radix sort the LBVH build uses: sorts n (key,value) pairs by key, stable.
  * HOST pointers; keys_out/vals_out may alias the inputs. */

@@ -350,6 +350,7 @@ def rt_lib():
         L.rt_trace_rays.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int,
                                     C.c_void_p]
         L.rt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+        L.rt_measure_fp32_tflops.argtypes = [C.c_int, C.POINTER(C.c_double)]
         L.rt_debug_sort_pairs.argtypes = [C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _rt = L
     return _rt
@@ -434,6 +435,12 @@ class Scene:
         s = Stats()
         _check(rt_lib().rt_get_stats(self._h, C.byref(s)))
         return s.as_dict()
+
+
+def measure_fp32_tflops(device_id: int = 0) -> float:
+    out = C.c_double()
+    _check(rt_lib().rt_measure_fp32_tflops(device_id, C.byref(out)))
+    return out.value
 
 
 def sort_pairs(keys: np.ndarray, vals: np.ndarray, device_id: int = 0):

@@ -373,6 +373,13 @@ int rt_get_stats(void* scene, rt_stats* out) {
   return RT_OK;
 }
 
+int rt_measure_fp32_tflops(int device_id, double* tflops_out) {
+  if (!tflops_out) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  if (rt_device_count() == 0) return fail(RT_ERR_NO_DEVICE, "no CUDA device: librt_b200 has no CPU fallback");
+  RT_CUDA_TRY(cudaSetDevice(device_id < 0 ? 0 : device_id), g_err);
+  return measure_fp32_tflops(tflops_out, g_err);
+}
+
 int rt_debug_sort_pairs(int device_id, uint64_t n, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                         uint32_t* vals_out) {
   if (n && (!keys_in || !vals_in || !keys_out || !vals_out)) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");

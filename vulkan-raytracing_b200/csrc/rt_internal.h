@@ -61,5 +61,6 @@ int pipeline_trace_batch(FramePipeline*, const SceneDev&, uint64_t n, const floa
 int assemble_shards(const FrameUniforms& U, uint32_t format, const void* gathered, void* frame, cudaStream_t,
                     std::string& err);
 int sm_count();
+int measure_fp32_tflops(double* tflops, std::string& err);
 
 }  // namespace rt

@@ -347,7 +347,7 @@ struct FramePipeline {
   unsigned long long* stats64 = nullptr;
   std::vector<uint32_t> h_cnt;
   cudaEvent_t ev[2] = {nullptr, nullptr};
-  int trace_blocks[3][2] = {{0, 0}, {0, 0}, {0, 0}}, shadow_blocks[3][2] = {{0, 0}, {0, 0}, {0, 0}};
+  std::vector<cudaEvent_t> kev;  // per bounce: trace begin/end, shadow begin/end
 };
 
 FramePipeline* pipeline_create() { return new FramePipeline(); }
@@ -364,6 +364,7 @@ void pipeline_destroy(FramePipeline* p) {
   pipeline_free_buffers(p);
   cudaFree(p->cnt); cudaFree(p->stats64);
   for (auto& e : p->ev) if (e) cudaEventDestroy(e);
+  for (auto& e : p->kev) cudaEventDestroy(e);
   delete p;
 }
 
@@ -392,6 +393,11 @@ static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std:
   if (!p->ev[0]) {
     RT_CUDA_TRY(cudaEventCreate(&p->ev[0]), err);
     RT_CUDA_TRY(cudaEventCreate(&p->ev[1]), err);
+  }
+  while (p->kev.size() < 4 * (bounces + 1)) {
+    cudaEvent_t e;
+    RT_CUDA_TRY(cudaEventCreate(&e), err);
+    p->kev.push_back(e);
   }
   return RT_OK;
 }
@@ -444,7 +450,9 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     k_trace<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->rayO[cur], p->rayD[cur], p->hits, p->qMiss, \
                                                     p->qDiff, p->qSpec, prim, p->stats64);                          \
   }
+    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 0], st), err);
     RT_DISPATCH_ACCEL(accel, counting, CALL_TRACE);
+    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 1], st), err);
 #undef CALL_TRACE
     k_shade_miss<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qMiss, p->rayO[cur], p->rayD[cur], p->sample);
     k_shade_diffuse<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qDiff, p->rayO[cur], p->rayD[cur], p->hits, p->shadowQ);
@@ -454,7 +462,9 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
     k_shadow<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64); \
   }
+    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 2], st), err);
     RT_DISPATCH_ACCEL(accel, counting, CALL_SHADOW);
+    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 3], st), err);
 #undef CALL_SHADOW
     launches += 4;
     last_bounce = j;
@@ -488,6 +498,16 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     float ms = 0.f;
     cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]);
     stats->frame_ms = ms;
+    double tr = 0.0, sh = 0.0;
+    for (uint32_t j = 0; j <= last_bounce; j++) {
+      float a = 0.f, b = 0.f;
+      cudaEventElapsedTime(&a, p->kev[4 * j + 0], p->kev[4 * j + 1]);
+      cudaEventElapsedTime(&b, p->kev[4 * j + 2], p->kev[4 * j + 3]);
+      tr += a; sh += b;
+    }
+    stats->trace_ms = tr;
+    stats->shadow_ms = sh;
+    stats->shade_ms = ms - tr - sh;
     stats->rays_primary = p->h_cnt[C_NRAY];
     stats->rays_secondary = stats->rays_shadow = stats->n_miss = stats->n_hit = 0;
     for (uint32_t j = 0; j <= last_bounce; j++) {
@@ -528,6 +548,44 @@ int pipeline_trace_batch(FramePipeline* p, const SceneDev& scene, uint64_t n, co
     stats->tris_tested = h64[1];
     stats->kernel_launches = 1;
   }
+  return RT_OK;
+}
+
+// FP32 FMA peak of the CUDA cores (denominator of the FLOP term of the traversal roofline):
+// 8 independent FMA chains per thread, enough resident warps to saturate the FMA pipes.
+__global__ void __launch_bounds__(256) k_fma_peak(float* out, int iters, float a, float b) {
+  float x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+      x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+    }
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+
+int measure_fp32_tflops(double* tflops, std::string& err) {
+  const int blocks = sm_count() * 8, threads = 256, iters = 4096;
+  float* d = nullptr;
+  RT_CUDA_TRY(cudaMalloc(&d, (size_t)blocks * threads * sizeof(float)), err);
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  double best = 0.0;
+  for (int rep = 0; rep < 5; rep++) {
+    cudaEventRecord(e0);
+    k_fma_peak<<<blocks, threads>>>(d, iters, 0.999f, 0.001f);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double fl = 2.0 * 64.0 * iters * (double)blocks * threads;
+    if (rep > 0 && ms > 0.f) best = std::max(best, fl / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(d);
+  RT_CUDA_TRY(cudaGetLastError(), err);
+  *tflops = best;
   return RT_OK;
 }
 

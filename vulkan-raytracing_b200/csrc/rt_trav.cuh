@@ -209,15 +209,16 @@ RT_HD bool trace_bvh2(const BlasDev& b, const RayObj& r, float tmin, uint32_t in
 //   n4 = (qhi_y[0..3], qhi_y[4..7], qhi_z[0..3], qhi_z[4..7])
 // child box = p + q * 2^(e-127).  meta: inner child = 0x20 | (24 + slot); leaf child =
 // (unary triangle count 1/3/7) << 5 | first-triangle offset from tri_base; empty = 0.
-RT_HD uint32_t byte_perm_lo(uint32_t w, int i) {
+// Byte i of w dropped into mantissa bits 8..15 of 1.0f: the float 1 + b * 2^-15, built with
+// one PRMT and no integer->float conversion.  The node test folds the "1 +" and the 2^-15
+// into its per-node constants, so each child plane costs one PRMT and one FFMA.
+RT_HD float byte2f_biased(uint32_t w, int i) {
 #if defined(__CUDA_ARCH__)
-  return __byte_perm(w, 0x4B000000u, 0x7650u | (uint32_t)i);
+  return __uint_as_float(__byte_perm(w, 0x3F800000u, 0x7604u | ((uint32_t)i << 4)));
 #else
-  return 0x4B000000u | ((w >> (8 * i)) & 0xFFu);
+  return u2f(0x3F800000u | (((w >> (8 * i)) & 0xFFu) << 8));
 #endif
 }
-// byte i of w as an exact float, without an integer->float conversion
-RT_HD float byte2f(uint32_t w, int i) { return u2f(byte_perm_lo(w, i)) - 8388608.0f; }
 
 RT_HD uint32_t sign_extend_s8x4(uint32_t x) { return ((x & 0x80808080u) >> 7) * 0xFFu; }
 
@@ -226,12 +227,21 @@ RT_HD uint32_t wide_node_test(const float4 n0, const uint4 n1, const uint4 n2, c
                               const RayObj& r, float tmin, float tmax) {
   const uint32_t e = f2u(n0.w);
   const float sx = u2f((e & 0xFFu) << 23), sy = u2f(((e >> 8) & 0xFFu) << 23), sz = u2f(((e >> 16) & 0xFFu) << 23);
-  // near planes shrink toward the origin, far planes grow: conservative against rounding
+  // plane t = q * a + b with a = 2^e / d, b = (p - o) / d.  With q carried as 1 + q*2^-15:
+  //   t = (1 + q*2^-15) * (a*2^15) + (b - a*2^15)
+  // Near planes are pulled toward the origin and far planes pushed away (factor 1 -+ 1e-5
+  // plus 0.01 grid cell), which covers every rounding in this decode: box
+  // culling only has to be conservative, the triangle test decides.
   const float ax = sx * r.idir.x, ay = sy * r.idir.y, az = sz * r.idir.z;
   const float bx = (n0.x - r.o.x) * r.idir.x, by = (n0.y - r.o.y) * r.idir.y, bz = (n0.z - r.o.z) * r.idir.z;
-  const float kn = 0.99999f, kf = 1.00001f;
-  const float anx = ax * kn, any_ = ay * kn, anz = az * kn, bnx = bx * kn, bny = by * kn, bnz = bz * kn;
-  const float afx = ax * kf, afy = ay * kf, afz = az * kf, bfx = bx * kf, bfy = by * kf, bfz = bz * kf;
+  const float kn = 0.99999f, kf = 1.00001f, cell = 0.01f;
+  const float Ax = ax * 32768.0f, Ay = ay * 32768.0f, Az = az * 32768.0f;
+  const float anx = Ax * kn, any_ = Ay * kn, anz = Az * kn;
+  const float afx = Ax * kf, afy = Ay * kf, afz = Az * kf;
+  const float bnx = fmaf(-cell, fabsf(ax), (bx - Ax) * kn), bny = fmaf(-cell, fabsf(ay), (by - Ay) * kn),
+              bnz = fmaf(-cell, fabsf(az), (bz - Az) * kn);
+  const float bfx = fmaf(cell, fabsf(ax), (bx - Ax) * kf), bfy = fmaf(cell, fabsf(ay), (by - Ay) * kf),
+              bfz = fmaf(cell, fabsf(az), (bz - Az) * kf);
   const bool px = r.d.x >= 0.0f, py = r.d.y >= 0.0f, pz = r.d.z >= 0.0f;
   uint32_t hitmask = 0;
 #pragma unroll
@@ -248,8 +258,10 @@ RT_HD uint32_t wide_node_test(const float4 n0, const uint4 n1, const uint4 n2, c
     const uint32_t nz = pz ? qloz : qhiz, fz = pz ? qhiz : qloz;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      float tnx = fmaf(byte2f(nx, j), anx, bnx), tny = fmaf(byte2f(ny, j), any_, bny), tnz = fmaf(byte2f(nz, j), anz, bnz);
-      float tfx = fmaf(byte2f(fx, j), afx, bfx), tfy = fmaf(byte2f(fy, j), afy, bfy), tfz = fmaf(byte2f(fz, j), afz, bfz);
+      float tnx = fmaf(byte2f_biased(nx, j), anx, bnx), tny = fmaf(byte2f_biased(ny, j), any_, bny),
+            tnz = fmaf(byte2f_biased(nz, j), anz, bnz);
+      float tfx = fmaf(byte2f_biased(fx, j), afx, bfx), tfy = fmaf(byte2f_biased(fy, j), afy, bfy),
+            tfz = fmaf(byte2f_biased(fz, j), afz, bfz);
       float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
       float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
       if (tn <= tf) {

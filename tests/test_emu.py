@@ -1,0 +1,154 @@
+"""The product's device functions (rt_build.cuh, rt_trav.cuh, rt_shade.cuh) compiled for the
+CPU (tests/emu) and checked against the oracle without a GPU: LBVH build, 8-wide collapse and
+compression, traversal, shading and the pixel-slot mapping of the wavefront pipeline."""
+import numpy as np
+import pytest
+
+import scenes
+
+
+def compare(rt, ob, emu, inputs, params, accel, cam=None):
+    cam = cam or rt.CameraVectors.default()
+    a = emu.EmuScene(inputs, accel).render(cam, params)
+    b = ob.OracleScene(inputs).render(cam, params, want=("rgba8", "rgba32f", "primary", "counts"))
+    for f in ("instance", "primitive", "t", "u", "v"):
+        assert np.array_equal(a["primary"][f], b["primary"][f]), f
+    assert np.array_equal(a["rgba32f"], b["rgba32f"])
+    assert np.array_equal(a["rgba8"], b["rgba8"])
+    for k in ("primary", "secondary", "shadow", "miss", "hit"):
+        assert a["counts"][k] == b["counts"][k], k
+    return a["counts"]
+
+
+@pytest.mark.parametrize("accel", [0, 1, 2])
+def test_smoke_scene_bit_exact(rt, ob, emu, accel):
+    compare(rt, ob, emu, scenes.smoke_scene(rt), rt.FrameParams.make(96, 72, 6, 3), accel)
+
+
+def test_standin_mesh_refraction_depth8(rt, ob, emu):
+    c = compare(rt, ob, emu, scenes.c3_scene(rt, level=4, sky_size=64), rt.FrameParams.make(160, 90, 8, 4), 0)
+    assert c["shadow"] > 0 and c["secondary"] > c["primary"] // 20
+
+
+def test_rotated_instances_and_camera(rt, ob, emu):
+    inputs = scenes.smoke_scene(rt)
+    xf = rt.orbit_transforms(0.61)
+    inputs.instances[0] = (0, rt.TYPE_REFRACTIVE, tuple(xf[1]))
+    cam = rt.Camera()
+    cam.processMouseMovement(-0.2, 0.1)
+    cam.move(rt.LEFT, 2.0)
+    compare(rt, ob, emu, inputs, rt.FrameParams.make(90, 60, 5, 2), 0, cam.vectors())
+
+
+def test_tiny_and_degenerate_meshes(rt, ob, emu):
+    cv, ci = scenes.unit_cube()
+    one = (np.array([[-3, -3, 0, 0, 0, 1], [3, -3, 0, 0, 0, 1], [0, 3, 0, 0, 0, 1]], np.float32),
+           np.array([[0, 1, 2]], np.uint32))
+    for accel in (0, 1, 2):
+        compare(rt, ob, emu, rt.SceneInputs([one], [(0, 0, rt.IDENTITY34)], None), rt.FrameParams.make(40, 30, 0, 1), accel)
+    two = (cv, ci[:2])
+    dup = (np.concatenate([cv, cv[:3]]), np.concatenate([ci, ci[:4], np.array([[0, 0, 1], [2, 2, 2]], np.uint32)]))
+    empty = (np.zeros((0, 6), np.float32), np.zeros((0, 3), np.uint32))
+    inputs = rt.SceneInputs([two, dup, empty], [(0, 1, rt.translation34(-3, 0, 0)), (1, 2, rt.IDENTITY34),
+                                                (2, 0, rt.IDENTITY34), (1, 7, rt.translation34(3, 0, 2))],
+                            scenes.sea_sky_64())
+    for accel in (0, 1):
+        compare(rt, ob, emu, inputs, rt.FrameParams.make(80, 60, 4, 2), accel)
+
+
+def decode_wide(nodes):
+    """-> list of (box lo, box hi, children) with children = (slot, kind, lo, hi, payload)."""
+    out = []
+    for w in nodes:
+        p = w[:3].copy().view(np.float32).astype(np.float64)
+        e = [(int(w[3]) >> s) & 0xFF for s in (0, 8, 16)]
+        imask = int(w[3]) >> 24
+        scale = np.array([2.0 ** (x - 127) for x in e])
+        child_base, tri_base = int(w[4]), int(w[5])
+        by = lambda a, b, i: (int(w[a if i < 4 else b]) >> (8 * (i & 3))) & 0xFF
+        kids, rank = [], 0
+        for s in range(8):
+            meta = by(6, 7, s)
+            if meta == 0:
+                continue
+            lo = p + scale * np.array([by(8, 9, s), by(10, 11, s), by(12, 13, s)])
+            hi = p + scale * np.array([by(14, 15, s), by(16, 17, s), by(18, 19, s)])
+            if imask & (1 << s):
+                assert meta == (0x20 | (24 + s))
+                kids.append((s, "node", lo, hi, child_base + rank))
+                rank += 1
+            else:
+                cnt = {1: 1, 3: 2, 7: 3}[meta >> 5]
+                kids.append((s, "leaf", lo, hi, (tri_base + (meta & 31), cnt)))
+        out.append(kids)
+    return out
+
+
+def test_wide_bvh_structure(rt, emu):
+    """Every triangle sits in exactly one leaf, every node is referenced exactly once, and each
+    quantised child box contains the geometry below it."""
+    v, i = rt.make_standin_armadillo(3)
+    es = emu.EmuScene(rt.SceneInputs([(v, i)], [(0, 0, rt.IDENTITY34)], None), 0)
+    nodes = es.wide_nodes(0)
+    tris = es.leaf_tris(0, i.shape[0])
+    prims = tris[:, 3].copy().view(np.uint32)
+    assert sorted(prims.tolist()) == list(range(i.shape[0]))
+    for k in range(i.shape[0]):
+        assert np.array_equal(tris[k, [0, 1, 2, 4, 5, 6, 8, 9, 10]].reshape(3, 3), v[i[prims[k]], :3])
+    kids = decode_wide(nodes)
+    seen_nodes, seen_tris = {0}, set()
+
+    def bounds(n):
+        lo, hi = np.full(3, np.inf), np.full(3, -np.inf)
+        for (_, kind, clo, chi, payload) in kids[n]:
+            if kind == "node":
+                assert payload not in seen_nodes
+                seen_nodes.add(payload)
+                blo, bhi = bounds(payload)
+            else:
+                first, cnt = payload
+                assert 1 <= cnt <= 3
+                ids = list(range(first, first + cnt))
+                assert not (seen_tris & set(ids))
+                seen_tris.update(ids)
+                pts = tris[ids][:, [0, 1, 2, 4, 5, 6, 8, 9, 10]].reshape(-1, 3)
+                blo, bhi = pts.min(0), pts.max(0)
+            assert np.all(clo <= blo + 1e-9) and np.all(chi >= bhi - 1e-9), "child box does not contain its geometry"
+            lo, hi = np.minimum(lo, blo), np.maximum(hi, bhi)
+        return lo, hi
+
+    bounds(0)
+    assert len(seen_nodes) == nodes.shape[0] and len(seen_tris) == i.shape[0]
+
+
+def test_trace_rays_matches_oracle_brute_force(rt, ob, emu):
+    inputs = scenes.c3_scene(rt, level=3, sky_size=8)
+    rng = np.random.default_rng(11)
+    n = 6000
+    o = rng.normal(0, 6, (n, 3)).astype(np.float32)
+    d = (rng.normal(0, 1.5, (n, 3)) + [0, 1, 2.5] - o).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    es, osc = emu.EmuScene(inputs, 0), ob.OracleScene(inputs)
+    for tmax in (10000.0, 7.0):
+        a, b = es.trace_rays(o, d, 0.001, tmax), osc.trace_rays(o, d, 0.001, tmax, brute=True)
+        for f in ("instance", "primitive", "t", "u", "v"):
+            assert np.array_equal(a[f], b[f])
+        a, b = es.trace_rays(o, d, 0.001, tmax, True), osc.trace_rays(o, d, 0.001, tmax, True, brute=True)
+        assert np.array_equal(a["instance"], b["instance"])
+
+
+@pytest.mark.parametrize("w,h,tw,th,n", [(200, 136, 32, 16, 3), (64, 64, 64, 64, 1), (70, 33, 8, 4, 4)])
+def test_slot_to_pixel_is_a_bijection(rt, emu, w, h, tw, th, n):
+    """Every pixel of the frame is owned by exactly one (shard, slot); padding slots map outside."""
+    import ctypes as C
+    seen = np.zeros((h, w), np.int32)
+    for s in range(n):
+        p = rt.FrameParams.make(w, h, 1, 1, tile_w=tw, tile_h=th, shard_index=s, shard_count=n)
+        tiles = ((w + tw - 1) // tw) * ((h + th - 1) // th)
+        local = (tiles - s + n - 1) // n if tiles > s else 0
+        for slot in range(local * tw * th):
+            ok, x, y = emu.slot_to_pixel(p, slot)
+            if ok:
+                seen[y, x] += 1
+                assert ((y // th) * ((w + tw - 1) // tw) + x // tw) % n == s
+    assert (seen == 1).all()

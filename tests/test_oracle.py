@@ -184,8 +184,8 @@ def test_shadow_ray_blocks_light(rt, ob):
     # a cube between the lit point and the light (5,5,5) along the light direction
     blocked = rt.SceneInputs([(v, np.array([[0, 1, 2]], np.uint32)), (cv, ci)],
                              [(0, 0, rt.IDENTITY34), (1, 0, rt.translation34(2.5, 2.5, 2.5))], None)
-    p = rt.FrameParams.make(1, 1, 0, 1)
-    img = ob.OracleScene(blocked).render(rt.CameraVectors.default(), p, want=("rgba32f", "counts"))
+    p = rt.FrameParams.make(101, 101, 0, 1)   # centre pixel: hit point within 0.1 of the origin
+    img = ob.OracleScene(blocked).render(rt.CameraVectors.default(), p, crop=(50, 50, 51, 51), want=("rgba32f", "counts"))
     assert img["counts"]["shadow"] == 1
     assert np.allclose(img["rgba32f"][0, 0, :3], [0.08, 0.24, 0.08], atol=1e-7)
 

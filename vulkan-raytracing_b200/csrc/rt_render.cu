@@ -19,9 +19,11 @@
 // bit-reproducible whatever order warps retire in.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "rt_internal.h"
+#include "rt_persist.cuh"
 
 namespace rt {
 
@@ -97,17 +99,67 @@ __global__ void __launch_bounds__(256) k_raygen(FrameUniforms U, uint32_t nslots
 }
 
 // ---- closest-hit traversal ----------------------------------------------------------------
+struct TraceSource {
+  const float4* rayO;
+  const float4* rayD;
+  __device__ __forceinline__ bool load(uint32_t idx, f3& o, f3& d, float& tmin, float& tmax) const {
+    const float4 ro = rayO[idx], rd = rayD[idx];
+    o = mk3(ro.x, ro.y, ro.z);
+    d = mk3(rd.x, rd.y, rd.z);
+    tmin = 0.001f;     // shader.rgen:87
+    tmax = 10000.0f;
+    return true;
+  }
+};
+
+// hit record + material-sorted queue append for the rays a warp has just finished
+struct TraceSink {
+  const SceneDev& scene;
+  const FrameUniforms& U;
+  uint32_t* cnt;
+  const float4* rayO;
+  uint4* hits;
+  uint32_t *qMiss, *qDiff, *qSpec;
+  rt_hit* primary;
+  __device__ __forceinline__ void done(bool finished, uint32_t idx, bool hit, const HitRec& h) const {
+    int kind = -1;
+    if (finished) {
+      hits[idx] = make_uint4(h.inst, h.prim, __float_as_uint(h.u), __float_as_uint(h.v));
+      kind = !hit ? 0 : (scene.inst[h.inst].type == 0u ? 1 : 2);
+      if (primary) {
+        const uint32_t s = __float_as_uint(rayO[idx].w);
+        uint32_t x, y;
+        slot_to_pixel(U, s / U.spp, x, y);
+        rt_hit out;
+        out.instance = h.inst; out.primitive = h.prim; out.t = hit ? h.t : 0.0f; out.u = h.u; out.v = h.v;
+        primary[((size_t)y * U.width + x) * U.spp + (s % U.spp)] = out;
+      }
+    }
+    uint32_t dst = warp_append(kind == 0, &cnt[C_NMISS]);
+    if (kind == 0) qMiss[dst] = idx;
+    dst = warp_append(kind == 1, &cnt[C_NDIFF]);
+    if (kind == 1) qDiff[dst] = idx;
+    dst = warp_append(kind == 2, &cnt[C_NSPEC]);
+    if (kind == 2) qSpec[dst] = idx;
+  }
+};
+
 template <int ACCEL, bool COUNT>
 __global__ void __launch_bounds__(TRACE_THREADS)
     k_trace(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ rayO,
             const float4* __restrict__ rayD, uint4* __restrict__ hits, uint32_t* __restrict__ qMiss,
             uint32_t* __restrict__ qDiff, uint32_t* __restrict__ qSpec, rt_hit* __restrict__ primary,
-            unsigned long long* __restrict__ stats64) {
+            unsigned long long* __restrict__ stats64, int refill_thresh, int tri_thresh) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NRAY];
+  if (ACCEL == ACCEL_WIDE && refill_thresh > 0) {  // RT_REFILL=0: run-to-completion loop
+    TraceSource src{rayO, rayD};
+    TraceSink sink{scene, U, cnt, rayO, hits, qMiss, qDiff, qSpec, primary};
+    trace_wide_persistent<false, COUNT>(scene, n, &cnt[C_WTRACE], st, src, sink, tc, refill_thresh, tri_thresh);
+  } else
   while (true) {
     uint32_t base = 0;
     if (lane_id() == 0) base = atomicAdd(&cnt[C_WTRACE], 32u);
@@ -191,15 +243,50 @@ __global__ void __launch_bounds__(256)
 }
 
 // ---- shadow rays + Phong ----------------------------------------------------------------------
+struct ShadowSource {
+  const FrameUniforms& U;
+  const float4* shadowQ;
+  __device__ __forceinline__ bool load(uint32_t i, f3& o, f3& d, float& tmin, float& tmax) const {
+    const float4 q0 = shadowQ[3 * (size_t)i], q1 = shadowQ[3 * (size_t)i + 1];
+    shadow_ray(U, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), o, d, tmax);
+    tmin = 0.001f;     // shader.rgen:112
+    return true;
+  }
+};
+
+struct ShadowSink {
+  const FrameUniforms& U;
+  const float4* shadowQ;
+  float4* sample;
+  __device__ __forceinline__ void done(bool finished, uint32_t i, bool occluded, const HitRec&) const {
+    if (finished && !occluded) {  // shader_shadow.rmiss ran: light the sample (shader.rgen:114-129)
+      const float4 q0 = shadowQ[3 * (size_t)i], q1 = shadowQ[3 * (size_t)i + 1], q2 = shadowQ[3 * (size_t)i + 2];
+      const f3 P = mk3(q0.x, q0.y, q0.z), N = mk3(q1.x, q1.y, q1.z);
+      f3 so, L;
+      float dist;
+      shadow_ray(U, P, N, so, L, dist);
+      const uint32_t s = __float_as_uint(q0.w);
+      const f3 c = phong(U, mk3(q2.x, q2.y, q2.z), N, L, s % U.spp);
+      sample[s] = make_float4(c.x, c.y, c.z, 1.0f);
+    }
+  }
+};
+
 template <int ACCEL, bool COUNT>
 __global__ void __launch_bounds__(TRACE_THREADS)
     k_shadow(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
-             float4* __restrict__ sample, unsigned long long* __restrict__ stats64) {
+             float4* __restrict__ sample, unsigned long long* __restrict__ stats64, int refill_thresh,
+             int tri_thresh) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NSHADOW];
+  if (ACCEL == ACCEL_WIDE && refill_thresh > 0) {  // RT_REFILL=0: run-to-completion loop
+    ShadowSource src{U, shadowQ};
+    ShadowSink sink{U, shadowQ, sample};
+    trace_wide_persistent<true, COUNT>(scene, n, &cnt[C_WSHADOW], st, src, sink, tc, refill_thresh, tri_thresh);
+  } else
   while (true) {
     uint32_t base = 0;
     if (lane_id() == 0) base = atomicAdd(&cnt[C_WSHADOW], 32u);
@@ -431,6 +518,9 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   if (rc != RT_OK) return rc;
   const uint32_t accel = rq.scene.accel;
   const bool counting = rq.counting;
+  // tuning knobs of the persistent traversal (defaults from the r02 sweep, profiles/)
+  static const int refill_t = getenv("RT_REFILL") ? atoi(getenv("RT_REFILL")) : 0;
+  static const int tri_t = getenv("RT_TRITHRESH") ? atoi(getenv("RT_TRITHRESH")) : 8;
   uint64_t launches = 0;
   RT_CUDA_TRY(cudaEventRecord(p->ev[0], st), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->cnt, 0, p->cnt_blocks * C_STRIDE * sizeof(uint32_t), st), err);
@@ -448,7 +538,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     static int blocks = 0;                                                                                          \
     if (!blocks) blocks = persistent_blocks(k_trace<A, C>, TRACE_THREADS);                                          \
     k_trace<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->rayO[cur], p->rayD[cur], p->hits, p->qMiss, \
-                                                    p->qDiff, p->qSpec, prim, p->stats64);                          \
+                                                    p->qDiff, p->qSpec, prim, p->stats64, refill_t, tri_t);         \
   }
     RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 0], st), err);
     RT_DISPATCH_ACCEL(accel, counting, CALL_TRACE);
@@ -460,7 +550,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   {                                                                                                       \
     static int blocks = 0;                                                                                \
     if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
-    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64); \
+    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, refill_t, tri_t); \
   }
     RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 2], st), err);
     RT_DISPATCH_ACCEL(accel, counting, CALL_SHADOW);

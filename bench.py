@@ -54,6 +54,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--accel", type=int, default=0, help="0 = compressed 8-wide BVH (product), 1 = binary LBVH cross-check")
     ap.add_argument("--sky", type=int, default=2048, help="procedural skybox face size")
     return ap.parse_args()
 
@@ -143,7 +144,7 @@ def load_peaks():
 def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix):
     """Algorithmic work of the traversal kernels (k_trace + k_shadow) of one frame, DESIGN.md §5."""
     n_node, n_tri = st_count["nodes_visited"], st_count["tris_tested"]
-    n_closest = st_count["rays_primary"] + st_count["rays_secondary"]
+    n_closest = st_count["rays_primary"] + st_count["rays_secondary"] - st_count.get("rays_top_level", 0)  # rays in the queue
     n_shadow = st_count["rays_shadow"]
     node_b, tri_b = st_count["node_bytes"], st_count["tri_bytes"]
     trav_bytes = n_node * node_b + n_tri * tri_b + n_closest * (32 + 16 + 4) + n_shadow * (48 + 16)
@@ -213,7 +214,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
     inputs = getattr(scenes, builder)(rt, sky_size=args.sky)
-    scene = rt.Scene(inputs, device_id=local_rank)
+    scene = rt.Scene(inputs, device_id=local_rank, accel=args.accel)
     build_ms = scene.stats()["build_ms"]
     scene.set_stream(torch.cuda.current_stream().cuda_stream)
     cam = rt.CameraVectors.default()

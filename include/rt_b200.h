@@ -155,6 +155,8 @@ typedef struct rt_stats {
   uint32_t tri_bytes;         /* bytes per leaf triangle of the active layout */
   uint32_t ray_state_bytes;   /* bytes of ray state written then read per ray */
   uint32_t reserved;
+  uint64_t rays_top_level;    /* of rays_primary: traces answered by the scene's top level (no
+                                 instance box reached), which never enter the ray queue */
 } rt_stats;
 
 /* --- library ---------------------------------------------------------------- */

@@ -24,7 +24,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 REPO_ROOT = os.path.dirname(_HERE)
-RT_LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+RT_LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 HOST_LIB_PATH = os.path.join(_HERE, "librt_host.so")
 
 TYPE_DIFFUSE, TYPE_MIRROR, TYPE_REFRACTIVE = 0, 1, 2
@@ -117,7 +117,7 @@ class Stats(C.Structure):
                 ("n_miss", C.c_uint64), ("n_hit", C.c_uint64), ("nodes_visited", C.c_uint64),
                 ("tris_tested", C.c_uint64), ("kernel_launches", C.c_uint64), ("bvh_nodes", C.c_uint64),
                 ("bvh_bytes", C.c_uint64), ("node_bytes", C.c_uint32), ("tri_bytes", C.c_uint32),
-                ("ray_state_bytes", C.c_uint32), ("reserved", C.c_uint32)]
+                ("ray_state_bytes", C.c_uint32), ("reserved", C.c_uint32), ("rays_top_level", C.c_uint64)]
 
     def as_dict(self) -> dict:
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}

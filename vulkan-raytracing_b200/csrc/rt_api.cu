@@ -37,6 +37,12 @@ struct Scene {
     s.sky = d_sky;
     s.sky_w = sky_w;
     s.sky_h = sky_h;
+    for (int k = 0; k < 3; k++) {
+      float lo = 3.0e38f, hi = -3.0e38f;
+      for (const InstDev& in : inst) { lo = std::min(lo, in.wlo[k]); hi = std::max(hi, in.whi[k]); }
+      s.slo[k] = inst.empty() ? 0.0f : lo;
+      s.sinv[k] = (!inst.empty() && hi > lo) ? 1.0f / (hi - lo) : 0.0f;
+    }
     return s;
   }
 };

@@ -166,6 +166,22 @@ RT_HD float half_area(float4 lo, float4 hi) {
 
 static const uint32_t WIDE_LEAF_MAX = 3;   // triangles per leaf child (unary count in 3 bits)
 
+// sorted positions of the (at most WIDE_LEAF_MAX) leaves below binary node `id`, left to right;
+// walks the subtree, so it does not rely on subtrees covering contiguous Morton ranges
+RT_HD uint32_t gather_leaves(const BuildArrays& a, int id, uint32_t* out) {
+  const int n = (int)a.ntri;
+  int stack[WIDE_LEAF_MAX + 1];
+  int sp = 0;
+  uint32_t c = 0;
+  stack[sp++] = id;
+  while (sp > 0) {
+    const int x = stack[--sp];
+    if (x >= n - 1) { if (c < WIDE_LEAF_MAX) out[c] = (uint32_t)(x - (n - 1)); c++; }
+    else { stack[sp++] = a.right[x]; stack[sp++] = a.left[x]; }
+  }
+  return c;
+}
+
 // biased exponent e such that extent / 2^(e-127) <= 255
 RT_HD uint32_t quant_exponent(float extent) {
   if (!(extent > 0.0f)) return 1u;
@@ -278,9 +294,10 @@ RT_HD void collapse_node(const BuildArrays& a, uint32_t w) {
       const uint32_t c = cnt[s];
       const uint32_t unary = c == 1 ? 1u : (c == 2 ? 3u : 7u);
       meta[wi] |= ((unary << 5) | tri_off) << sh;
-      const uint32_t first = id >= n - 1 ? (uint32_t)(id - (n - 1)) : a.first[id];
+      uint32_t leafpos[WIDE_LEAF_MAX];
+      gather_leaves(a, id, leafpos);
       for (uint32_t k = 0; k < c; k++) {
-        const uint32_t prim = a.vals[first + k];
+        const uint32_t prim = a.vals[leafpos[k]];
         const f3 p0 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)prim]));
         const f3 p1 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)prim + 1]));
         const f3 p2 = load_pos(a.verts, RT_LDG(&a.idx[3 * (size_t)prim + 2]));

@@ -39,6 +39,21 @@ static inline uint2 make_uint2(uint32_t x, uint32_t y) { return uint2{x, y}; }
 
 namespace rt {
 
+// 32-byte load: one LDG.E.ENL2.256 on sm_100a (half the load instructions and L1 wavefronts of
+// two 128-bit loads); plain loads in the CPU emulation build.  p must be 32-byte aligned.
+struct float8 { float4 a, b; };
+RT_HD float8 ldg256(const float4* p) {
+  float8 r;
+#if defined(__CUDA_ARCH__)
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(r.a.x), "=f"(r.a.y), "=f"(r.a.z), "=f"(r.a.w), "=f"(r.b.x), "=f"(r.b.y), "=f"(r.b.z), "=f"(r.b.w)
+               : "l"(p));
+#else
+  r.a = p[0]; r.b = p[1];
+#endif
+  return r;
+}
+
 RT_HD uint32_t f2u(float f) {
 #if defined(__CUDA_ARCH__)
   return __float_as_uint(f);

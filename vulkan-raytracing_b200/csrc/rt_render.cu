@@ -24,10 +24,11 @@
 
 #include "rt_internal.h"
 #include "rt_persist.cuh"
+#include "rt_wave.cuh"
 
 namespace rt {
 
-enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_STRIDE = 16 };
+enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_NCULL, C_STRIDE = 16 };
 constexpr int TRACE_THREADS = 128;
 constexpr int STACK_SM = 8;      // stack entries per thread kept in shared memory
 constexpr int STACK_LOCAL = 56;  // overflow entries in local memory
@@ -73,29 +74,58 @@ __device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t* counter) {
 }
 
 // ---- ray generation ---------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_raygen(FrameUniforms U, uint32_t nslots, float4* __restrict__ rayO,
+// A primary ray that reaches no instance's padded world box is answered here, at the top level
+// of the scene (what the TLAS does for traceRayEXT): the miss shader's sky lookup runs at once and
+// the ray never enters the queue.  Only rays with something to traverse are written to HBM.
+__global__ void __launch_bounds__(256) k_raygen(SceneDev scene, FrameUniforms U, uint32_t nslots, float4* __restrict__ rayO,
                                                 float4* __restrict__ rayD, float4* __restrict__ sample,
-                                                uint32_t* __restrict__ cnt) {
+                                                uint32_t* __restrict__ cnt, rt_hit* __restrict__ primary) {
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const f3 amb = ambient_color();
+  uint32_t culled = 0;
   for (uint64_t base = (uint64_t)w * 32; base < nslots; base += (uint64_t)warps * 32) {
     const uint32_t s = (uint32_t)base + lane_id();
-    bool valid = false;
+    bool valid = false, reach = false;
     f3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
     if (s < nslots) {
       uint32_t x, y;
       valid = slot_to_pixel(U, s / U.spp, x, y);
-      // every sample starts as tmpColor = Iamb*ka (shader.rgen:81); padding stays 0
-      sample[s] = valid ? make_float4(amb.x, amb.y, amb.z, 1.0f) : make_float4(0.f, 0.f, 0.f, 0.f);
-      if (valid) raygen(U, x, y, s % U.spp, o, d);
+      if (valid) {
+        raygen(U, x, y, s % U.spp, o, d);
+        RayObj rw;
+        rw.o = o;
+        rw.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
+        for (uint32_t i = 0; i < scene.n_inst && !reach; i++) {
+          const InstDev& in = scene.inst[i];
+          reach = slab_test(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], 0.001f, 10000.0f);
+        }
+        if (reach) {
+          // every sample starts as tmpColor = Iamb*ka (shader.rgen:81)
+          sample[s] = make_float4(amb.x, amb.y, amb.z, 1.0f);
+        } else {
+          const f3 c = sky_sample(scene, mk3(d.x, d.y, -d.z));  // shader.rmiss + shader.rgen:90-94
+          sample[s] = make_float4(c.x, c.y, c.z, 1.0f);
+          culled++;
+          if (primary) {
+            rt_hit out;
+            out.instance = RT_MISS; out.primitive = RT_MISS; out.t = 0.0f; out.u = 0.0f; out.v = 0.0f;
+            primary[((size_t)y * U.width + x) * U.spp + (s % U.spp)] = out;
+          }
+        }
+      } else {
+        sample[s] = make_float4(0.f, 0.f, 0.f, 0.f);  // padding outside the frame
+      }
     }
-    const uint32_t dst = warp_append(valid, &cnt[C_NRAY]);
-    if (valid) {
+    const uint32_t dst = warp_append(reach, &cnt[C_NRAY]);
+    if (reach) {
       rayO[dst] = make_float4(o.x, o.y, o.z, __uint_as_float(s));
       rayD[dst] = make_float4(d.x, d.y, d.z, 0.0f);
     }
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) culled += __shfl_xor_sync(0xFFFFFFFFu, culled, o);
+  if (lane_id() == 0 && culled) atomicAdd(&cnt[C_NCULL], culled);
 }
 
 // ---- closest-hit traversal ----------------------------------------------------------------
@@ -144,29 +174,38 @@ struct TraceSink {
   }
 };
 
+// 8 CTAs x 4 warps per SM (64 registers): the traversal is latency- and issue-bound, and 32
+// resident warps beat the 20 a 96-register build allows (profiles/r01_sweep_occupancy.txt)
+#ifndef RT_TRACE_MINBLK
+#define RT_TRACE_MINBLK 8
+#endif
+#define RT_TRACE_BOUNDS __launch_bounds__(TRACE_THREADS, RT_TRACE_MINBLK)
 template <int ACCEL, bool COUNT>
-__global__ void __launch_bounds__(TRACE_THREADS)
+__global__ void RT_TRACE_BOUNDS
     k_trace(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ rayO,
             const float4* __restrict__ rayD, uint4* __restrict__ hits, uint32_t* __restrict__ qMiss,
             uint32_t* __restrict__ qDiff, uint32_t* __restrict__ qSpec, rt_hit* __restrict__ primary,
-            unsigned long long* __restrict__ stats64, int refill_thresh, int tri_thresh) {
+            unsigned long long* __restrict__ stats64, int refill_thresh, int tri_thresh,
+            const uint32_t* __restrict__ perm) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NRAY];
+#ifdef RT_WITH_PERSIST
   if (ACCEL == ACCEL_WIDE && refill_thresh > 0) {  // RT_REFILL=0: run-to-completion loop
     TraceSource src{rayO, rayD};
     TraceSink sink{scene, U, cnt, rayO, hits, qMiss, qDiff, qSpec, primary};
     trace_wide_persistent<false, COUNT>(scene, n, &cnt[C_WTRACE], st, src, sink, tc, refill_thresh, tri_thresh);
   } else
+#endif
   while (true) {
     uint32_t base = 0;
     if (lane_id() == 0) base = atomicAdd(&cnt[C_WTRACE], 32u);
     base = __shfl_sync(0xFFFFFFFFu, base, 0);
     if (base >= n) break;
-    const uint32_t idx = base + lane_id();
-    const bool active = idx < n;
+    const bool active = base + lane_id() < n;
+    const uint32_t idx = (perm && active) ? perm[base + lane_id()] : base + lane_id();
     int kind = -1;  // 0 miss, 1 diffuse, 2 specular/other
     if (active) {
       const float4 ro = rayO[idx], rd = rayD[idx];
@@ -273,7 +312,7 @@ struct ShadowSink {
 };
 
 template <int ACCEL, bool COUNT>
-__global__ void __launch_bounds__(TRACE_THREADS)
+__global__ void RT_TRACE_BOUNDS
     k_shadow(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
              float4* __restrict__ sample, unsigned long long* __restrict__ stats64, int refill_thresh,
              int tri_thresh) {
@@ -282,11 +321,13 @@ __global__ void __launch_bounds__(TRACE_THREADS)
   st.sm = &stack_sm[threadIdx.x];
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NSHADOW];
+#ifdef RT_WITH_PERSIST
   if (ACCEL == ACCEL_WIDE && refill_thresh > 0) {  // RT_REFILL=0: run-to-completion loop
     ShadowSource src{U, shadowQ};
     ShadowSink sink{U, shadowQ, sample};
     trace_wide_persistent<true, COUNT>(scene, n, &cnt[C_WSHADOW], st, src, sink, tc, refill_thresh, tri_thresh);
   } else
+#endif
   while (true) {
     uint32_t base = 0;
     if (lane_id() == 0) base = atomicAdd(&cnt[C_WSHADOW], 32u);
@@ -314,11 +355,129 @@ __global__ void __launch_bounds__(TRACE_THREADS)
   }
 }
 
+// ---- warp-synchronous variants (rt_wave.cuh) ---------------------------------------------------
+struct WaveTraceSource {
+  const float4* rayO;
+  const float4* rayD;
+  const uint32_t* perm;
+  __device__ __forceinline__ void load(uint32_t i, f3& o, f3& d, float& tmax) const {
+    const uint32_t idx = perm ? perm[i] : i;
+    const float4 ro = rayO[idx], rd = rayD[idx];
+    o = mk3(ro.x, ro.y, ro.z);
+    d = mk3(rd.x, rd.y, rd.z);
+    tmax = 10000.0f;   // shader.rgen:87
+  }
+};
+
+struct WaveTraceSink {
+  const SceneDev& scene;
+  const FrameUniforms& U;
+  uint32_t* cnt;
+  const float4* rayO;
+  const uint32_t* perm;
+  uint4* hits;
+  uint32_t *qMiss, *qDiff, *qSpec;
+  rt_hit* primary;
+  __device__ __forceinline__ void done(bool finished, uint32_t i, bool hit, const HitRec& h) const {
+    int kind = -1;
+    uint32_t idx = 0;
+    if (finished) {
+      idx = perm ? perm[i] : i;
+      hits[idx] = make_uint4(h.inst, h.prim, __float_as_uint(h.u), __float_as_uint(h.v));
+      kind = !hit ? 0 : (scene.inst[h.inst].type == 0u ? 1 : 2);
+      if (primary) {
+        const uint32_t s = __float_as_uint(rayO[idx].w);
+        uint32_t x, y;
+        slot_to_pixel(U, s / U.spp, x, y);
+        rt_hit out;
+        out.instance = h.inst; out.primitive = h.prim; out.t = hit ? h.t : 0.0f; out.u = h.u; out.v = h.v;
+        primary[((size_t)y * U.width + x) * U.spp + (s % U.spp)] = out;
+      }
+    }
+    uint32_t dst = warp_append(kind == 0, &cnt[C_NMISS]);
+    if (kind == 0) qMiss[dst] = idx;
+    dst = warp_append(kind == 1, &cnt[C_NDIFF]);
+    if (kind == 1) qDiff[dst] = idx;
+    dst = warp_append(kind == 2, &cnt[C_NSPEC]);
+    if (kind == 2) qSpec[dst] = idx;
+  }
+};
+
+template <bool COUNT>
+__global__ void RT_TRACE_BOUNDS
+    k_trace_wave(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ rayO,
+                 const float4* __restrict__ rayD, uint4* __restrict__ hits, uint32_t* __restrict__ qMiss,
+                 uint32_t* __restrict__ qDiff, uint32_t* __restrict__ qSpec, rt_hit* __restrict__ primary,
+                 unsigned long long* __restrict__ stats64, int refill_min, int tri_min, const uint32_t* __restrict__ perm) {
+  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  HybridStack st;
+  st.sm = &stack_sm[threadIdx.x];
+  TravCounters tc{0ull, 0ull};
+  const WaveTraceSource src{rayO, rayD, perm};
+  const WaveTraceSink sink{scene, U, cnt, rayO, perm, hits, qMiss, qDiff, qSpec, primary};
+  wave_trace<false, COUNT>(scene, cnt[C_NRAY], &cnt[C_WTRACE], st, src, sink, tc, refill_min, tri_min);
+  if (COUNT) {
+    atomicAdd(&stats64[0], tc.nodes);
+    atomicAdd(&stats64[1], tc.tris);
+  }
+}
+
+struct WaveShadowSource {
+  const FrameUniforms& U;
+  const float4* shadowQ;
+  __device__ __forceinline__ void load(uint32_t i, f3& o, f3& d, float& tmax) const {
+    const float4 q0 = shadowQ[3 * (size_t)i], q1 = shadowQ[3 * (size_t)i + 1];
+    shadow_ray(U, mk3(q0.x, q0.y, q0.z), mk3(q1.x, q1.y, q1.z), o, d, tmax);
+  }
+};
+
+template <bool COUNT>
+__global__ void RT_TRACE_BOUNDS
+    k_shadow_wave(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
+                  float4* __restrict__ sample, unsigned long long* __restrict__ stats64, int refill_min, int tri_min) {
+  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  HybridStack st;
+  st.sm = &stack_sm[threadIdx.x];
+  TravCounters tc{0ull, 0ull};
+  const WaveShadowSource src{U, shadowQ};
+  const ShadowSink sink{U, shadowQ, sample};
+  wave_trace<true, COUNT>(scene, cnt[C_NSHADOW], &cnt[C_WSHADOW], st, src, sink, tc, refill_min, tri_min);
+  if (COUNT) {
+    atomicAdd(&stats64[2], tc.nodes);
+    atomicAdd(&stats64[3], tc.tris);
+  }
+}
+
+// Sort key of a secondary ray: 21-bit Morton cell of the origin inside the scene bounds, then
+// a 9-bit Morton cell of the direction.  Rays of one warp then start close together and head
+// the same way, so they visit the same nodes and finish after a similar number of steps.
+__device__ __forceinline__ uint32_t spread3_10(uint32_t v) {
+  v &= 0x3FFu;
+  v = (v | (v << 16)) & 0x030000FFu;
+  v = (v | (v << 8)) & 0x0300F00Fu;
+  v = (v | (v << 4)) & 0x030C30C3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+__device__ __forceinline__ uint64_t ray_sort_key(const SceneDev& s, f3 o, f3 d) {
+  const float cx = fminf(fmaxf((o.x - s.slo[0]) * s.sinv[0], 0.0f), 0.9999f);
+  const float cy = fminf(fmaxf((o.y - s.slo[1]) * s.sinv[1], 0.0f), 0.9999f);
+  const float cz = fminf(fmaxf((o.z - s.slo[2]) * s.sinv[2], 0.0f), 0.9999f);
+  const uint32_t om = (spread3_10((uint32_t)(cx * 128.0f)) << 2) | (spread3_10((uint32_t)(cy * 128.0f)) << 1) |
+                      spread3_10((uint32_t)(cz * 128.0f));
+  const float il = 1.0f / (fabsf(d.x) + fabsf(d.y) + fabsf(d.z) + 1e-30f);
+  const uint32_t qx = (uint32_t)fminf(fmaf(d.x * il, 4.0f, 4.0f), 7.0f), qy = (uint32_t)fminf(fmaf(d.y * il, 4.0f, 4.0f), 7.0f),
+                 qz = (uint32_t)fminf(fmaf(d.z * il, 4.0f, 4.0f), 7.0f);
+  const uint32_t dm = (spread3_10(qx) << 2) | (spread3_10(qy) << 1) | spread3_10(qz);
+  return ((uint64_t)om << 9) | (uint64_t)(dm & 0x1FFu);
+}
+
 // ---- mirror / refraction: next bounce ----------------------------------------------------------
 __global__ void __launch_bounds__(256)
     k_shade_spec(SceneDev scene, const uint32_t* __restrict__ cnt, uint32_t* __restrict__ cntNext,
                  const uint32_t* __restrict__ qSpec, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
-                 const uint4* __restrict__ hits, float4* __restrict__ nextO, float4* __restrict__ nextD) {
+                 const uint4* __restrict__ hits, float4* __restrict__ nextO, float4* __restrict__ nextD,
+                 uint64_t* __restrict__ skeys, uint32_t* __restrict__ svals) {
   const uint32_t n = cnt[C_NSPEC];
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -342,6 +501,10 @@ __global__ void __launch_bounds__(256)
     if (active) {
       nextO[dst] = make_float4(o.x, o.y, o.z, slot);
       nextD[dst] = make_float4(d.x, d.y, d.z, 0.0f);
+      if (skeys) {
+        skeys[dst] = ray_sort_key(scene, o, d);
+        svals[dst] = dst;
+      }
     }
   }
 }
@@ -429,6 +592,9 @@ struct FramePipeline {
   uint32_t *qMiss = nullptr, *qDiff = nullptr, *qSpec = nullptr;
   float4* shadowQ = nullptr;
   float4* sample = nullptr;
+  uint64_t* sortK[2] = {nullptr, nullptr};
+  uint32_t* sortV[2] = {nullptr, nullptr};
+  uint32_t* sortH = nullptr;
   uint32_t* cnt = nullptr;
   size_t cnt_blocks = 0;
   unsigned long long* stats64 = nullptr;
@@ -442,6 +608,8 @@ FramePipeline* pipeline_create() { return new FramePipeline(); }
 static void pipeline_free_buffers(FramePipeline* p) {
   for (int i = 0; i < 2; i++) { cudaFree(p->rayO[i]); cudaFree(p->rayD[i]); p->rayO[i] = p->rayD[i] = nullptr; }
   cudaFree(p->hits); cudaFree(p->qMiss); cudaFree(p->qDiff); cudaFree(p->qSpec); cudaFree(p->shadowQ); cudaFree(p->sample);
+  for (int i = 0; i < 2; i++) { cudaFree(p->sortK[i]); cudaFree(p->sortV[i]); p->sortK[i] = nullptr; p->sortV[i] = nullptr; }
+  cudaFree(p->sortH); p->sortH = nullptr;
   p->hits = nullptr; p->qMiss = p->qDiff = p->qSpec = nullptr; p->shadowQ = nullptr; p->sample = nullptr;
   p->cap = 0;
 }
@@ -468,6 +636,11 @@ static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std:
     RT_CUDA_TRY(cudaMalloc(&p->qSpec, slots * sizeof(uint32_t)), err);
     RT_CUDA_TRY(cudaMalloc(&p->shadowQ, slots * 3 * sizeof(float4)), err);
     RT_CUDA_TRY(cudaMalloc(&p->sample, slots * sizeof(float4)), err);
+    for (int i = 0; i < 2; i++) {
+      RT_CUDA_TRY(cudaMalloc(&p->sortK[i], slots * sizeof(uint64_t)), err);
+      RT_CUDA_TRY(cudaMalloc(&p->sortV[i], slots * sizeof(uint32_t)), err);
+    }
+    RT_CUDA_TRY(cudaMalloc(&p->sortH, sort_hist_words(slots) * sizeof(uint32_t)), err);
     p->cap = slots;
   }
   if (bounces + 2 > p->cnt_blocks) {
@@ -521,11 +694,18 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   // tuning knobs of the persistent traversal (defaults from the r02 sweep, profiles/)
   static const int refill_t = getenv("RT_REFILL") ? atoi(getenv("RT_REFILL")) : 0;
   static const int tri_t = getenv("RT_TRITHRESH") ? atoi(getenv("RT_TRITHRESH")) : 8;
+  static const int sort_from = getenv("RT_SORT_FROM") ? atoi(getenv("RT_SORT_FROM")) : 1000;
+  static const int sort_bits = getenv("RT_SORT_BITS") ? atoi(getenv("RT_SORT_BITS")) : 30;
+  static const bool wave_on = getenv("RT_WAVE") ? atoi(getenv("RT_WAVE")) != 0 : false;
+  static const int wave_refill = getenv("RT_WAVE_REFILL") ? atoi(getenv("RT_WAVE_REFILL")) : 12;
+  static const int wave_tri = getenv("RT_WAVE_TRI") ? atoi(getenv("RT_WAVE_TRI")) : 6;
+  const uint32_t* perm = nullptr;
   uint64_t launches = 0;
   RT_CUDA_TRY(cudaEventRecord(p->ev[0], st), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->cnt, 0, p->cnt_blocks * C_STRIDE * sizeof(uint32_t), st), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
-  k_raygen<<<stride_blocks(nslots, 256), 256, 0, st>>>(U, (uint32_t)nslots, p->rayO[0], p->rayD[0], p->sample, p->cnt);
+  k_raygen<<<stride_blocks(nslots, 256), 256, 0, st>>>(rq.scene, U, (uint32_t)nslots, p->rayO[0], p->rayD[0], p->sample, p->cnt,
+                                                       rq.want_primary ? rq.d_primary : nullptr);
   launches++;
   int cur = 0;
   uint32_t last_bounce = 0;
@@ -538,9 +718,16 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     static int blocks = 0;                                                                                          \
     if (!blocks) blocks = persistent_blocks(k_trace<A, C>, TRACE_THREADS);                                          \
     k_trace<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->rayO[cur], p->rayD[cur], p->hits, p->qMiss, \
-                                                    p->qDiff, p->qSpec, prim, p->stats64, refill_t, tri_t);         \
+                                                    p->qDiff, p->qSpec, prim, p->stats64, refill_t, tri_t, perm);   \
   }
     RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 0], st), err);
+    const bool wave = accel == ACCEL_WIDE && wave_on && rq.scene.n_inst <= 32u;
+    if (wave) {
+      static int wb[2] = {0, 0};
+      if (!wb[0]) { wb[0] = persistent_blocks(k_trace_wave<false>, TRACE_THREADS); wb[1] = persistent_blocks(k_trace_wave<true>, TRACE_THREADS); }
+      if (counting) k_trace_wave<true><<<wb[1], TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->rayO[cur], p->rayD[cur], p->hits, p->qMiss, p->qDiff, p->qSpec, prim, p->stats64, wave_refill, wave_tri, perm);
+      else k_trace_wave<false><<<wb[0], TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->rayO[cur], p->rayD[cur], p->hits, p->qMiss, p->qDiff, p->qSpec, prim, p->stats64, wave_refill, wave_tri, perm);
+    } else
     RT_DISPATCH_ACCEL(accel, counting, CALL_TRACE);
     RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 1], st), err);
 #undef CALL_TRACE
@@ -553,22 +740,37 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     k_shadow<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, refill_t, tri_t); \
   }
     RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 2], st), err);
+    if (wave) {
+      static int wb[2] = {0, 0};
+      if (!wb[0]) { wb[0] = persistent_blocks(k_shadow_wave<false>, TRACE_THREADS); wb[1] = persistent_blocks(k_shadow_wave<true>, TRACE_THREADS); }
+      if (counting) k_shadow_wave<true><<<wb[1], TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
+      else k_shadow_wave<false><<<wb[0], TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
+    } else
     RT_DISPATCH_ACCEL(accel, counting, CALL_SHADOW);
     RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 3], st), err);
 #undef CALL_SHADOW
     launches += 4;
     last_bounce = j;
     if (j < U.max_bounce) {
+      const bool sorting = accel == ACCEL_WIDE && (int)(j + 1) >= sort_from;
       k_shade_spec<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, cn, p->qSpec, p->rayO[cur], p->rayD[cur], p->hits,
-                                                   p->rayO[cur ^ 1], p->rayD[cur ^ 1]);
+                                                   p->rayO[cur ^ 1], p->rayD[cur ^ 1], sorting ? p->sortK[0] : nullptr,
+                                                   sorting ? p->sortV[0] : nullptr);
       launches++;
       cur ^= 1;
+      perm = nullptr;
       // deep bounce limits (MAX_BOUNCE_COUNT 63): stop as soon as no ray survives
-      if (j >= 3) {
+      if (j >= 3 || sorting) {
         uint32_t alive = 0;
         RT_CUDA_TRY(cudaMemcpyAsync(&alive, cn + C_NRAY, sizeof alive, cudaMemcpyDeviceToHost, st), err);
         RT_CUDA_TRY(cudaStreamSynchronize(st), err);
         if (alive == 0) break;
+        if (sorting) {
+          int rc2 = sort_pairs(p->sortK[0], p->sortK[1], p->sortV[0], p->sortV[1], alive, sort_bits, p->sortH, st, err);
+          if (rc2 != RT_OK) return rc2;
+          launches += 3 * (((sort_bits + 7) / 8 + 1) & ~1);
+          perm = p->sortV[0];
+        }
       }
     }
   }
@@ -596,10 +798,24 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
       tr += a; sh += b;
     }
     stats->trace_ms = tr;
+    static const bool dbg = getenv("RT_DEBUG_BOUNCES") != nullptr;
+    if (dbg) {
+      for (uint32_t j = 0; j <= last_bounce; j++) {
+        float a = 0.f, b = 0.f;
+        cudaEventElapsedTime(&a, p->kev[4 * j + 0], p->kev[4 * j + 1]);
+        cudaEventElapsedTime(&b, p->kev[4 * j + 2], p->kev[4 * j + 3]);
+        const uint32_t* c = &p->h_cnt[(size_t)j * C_STRIDE];
+        fprintf(stderr, "bounce %u: trace %.3f ms shadow %.3f ms  rays %u miss %u diff %u spec %u shadow %u\n", j, a, b,
+                c[C_NRAY], c[C_NMISS], c[C_NDIFF], c[C_NSPEC], c[C_NSHADOW]);
+      }
+    }
     stats->shadow_ms = sh;
     stats->shade_ms = ms - tr - sh;
-    stats->rays_primary = p->h_cnt[C_NRAY];
-    stats->rays_secondary = stats->rays_shadow = stats->n_miss = stats->n_hit = 0;
+    // primary traces = rays traversed + rays the top level answered in k_raygen
+    stats->rays_primary = (uint64_t)p->h_cnt[C_NRAY] + p->h_cnt[C_NCULL];
+    stats->rays_secondary = stats->rays_shadow = stats->n_hit = 0;
+    stats->n_miss = p->h_cnt[C_NCULL];
+    stats->rays_top_level = p->h_cnt[C_NCULL];
     for (uint32_t j = 0; j <= last_bounce; j++) {
       const uint32_t* c = &p->h_cnt[(size_t)j * C_STRIDE];
       if (j > 0) stats->rays_secondary += c[C_NRAY];

@@ -42,6 +42,7 @@ struct SceneDev {
   uint32_t accel;
   const uint8_t* sky;  // 6 x h x w x RGBA8
   uint32_t sky_w, sky_h;
+  float slo[3], sinv[3];  // world bounds of all instances (origin cell of the ray sort key)
 };
 
 struct HitRec {
@@ -166,6 +167,19 @@ RT_HD bool slab_test(const RayObj& r, float lox, float loy, float loz, float hix
 // ---- binary LBVH (cross-check path) -----------------------------------------------------
 // node = 4 x float4: (c0.lo.xyz, c0.hi.x) (c0.hi.yz, c1.lo.xy) (c1.lo.z, c1.hi.xyz)
 //                    (child0, child1, -, -) as int bits; child < 0: leaf, triangle slot ~child
+// interval of the ray inside an explicit box; the relative margins on the two results cover
+// the rounding of (plane - o) * idir (each plane t has relative error <= 2^-23)
+RT_HD void slab_interval(const RayObj& r, float lox, float loy, float loz, float hix, float hiy, float hiz, float tmin,
+                         float tmax, float& tn, float& tf) {
+  const float t1x = (lox - r.o.x) * r.idir.x, t2x = (hix - r.o.x) * r.idir.x;
+  const float t1y = (loy - r.o.y) * r.idir.y, t2y = (hiy - r.o.y) * r.idir.y;
+  const float t1z = (loz - r.o.z) * r.idir.z, t2z = (hiz - r.o.z) * r.idir.z;
+  const float n = fmaxf(fmaxf(fminf(t1x, t2x), fminf(t1y, t2y)), fminf(t1z, t2z));
+  const float f = fminf(fminf(fmaxf(t1x, t2x), fmaxf(t1y, t2y)), fmaxf(t1z, t2z));
+  tn = fmaxf(n * 0.99999f, tmin);
+  tf = fminf(f * 1.00001f, tmax);
+}
+
 template <class Stack, bool ANY, bool COUNT>
 RT_HD bool trace_bvh2(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
                       TravCounters* cnt) {
@@ -174,28 +188,32 @@ RT_HD bool trace_bvh2(const BlasDev& b, const RayObj& r, float tmin, uint32_t in
   st.reset();
   int node = 0;
   while (true) {
-    const float4 n0 = RT_LDG(&b.nodes[4 * (size_t)node + 0]);
-    const float4 n1 = RT_LDG(&b.nodes[4 * (size_t)node + 1]);
-    const float4 n2 = RT_LDG(&b.nodes[4 * (size_t)node + 2]);
-    const float4 n3 = RT_LDG(&b.nodes[4 * (size_t)node + 3]);
+    if (node < 0) {
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
+      if (st.empty()) break;
+      node = (int)st.pop().x;
+      continue;
+    }
+    const float8 lo8 = ldg256(&b.nodes[4 * (size_t)node]), hi8 = ldg256(&b.nodes[4 * (size_t)node + 2]);
+    const float4 n0 = lo8.a, n1 = lo8.b, n2 = hi8.a, n3 = hi8.b;
     if (COUNT) cnt->nodes++;
-    bool h0 = slab_test(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t);
-    bool h1 = slab_test(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t);
+    float tn0, tf0, tn1, tf1;
+    slab_interval(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
+    slab_interval(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
+    const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
     int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
-    int next = -1;
-    bool have = false;
-    if (h0) {
-      if (c0 < 0) { if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~c0, r, tmin, inst, best, cnt)) return true; }
-      else { next = c0; have = true; }
+    if (h0 && h1) {
+      if (tn1 < tn0) { const int t = c0; c0 = c1; c1 = t; }
+      st.push(make_uint2((uint32_t)c1, 0u));
+      node = c0;
+    } else if (h0) {
+      node = c0;
+    } else if (h1) {
+      node = c1;
+    } else {
+      if (st.empty()) break;
+      node = (int)st.pop().x;
     }
-    if (h1) {
-      if (c1 < 0) { if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~c1, r, tmin, inst, best, cnt)) return true; }
-      else if (have) st.push(make_uint2((uint32_t)c1, 0u));
-      else { next = c1; have = true; }
-    }
-    if (have) { node = next; continue; }
-    if (st.empty()) break;
-    node = (int)st.pop().x;
   }
   return false;
 }
@@ -217,6 +235,14 @@ RT_HD float byte2f_biased(uint32_t w, int i) {
   return __uint_as_float(__byte_perm(w, 0x3F800000u, 0x7604u | ((uint32_t)i << 4)));
 #else
   return u2f(0x3F800000u | (((w >> (8 * i)) & 0xFFu) << 8));
+#endif
+}
+
+RT_HD uint32_t byte_of(uint32_t w, int i) {
+#if defined(__CUDA_ARCH__)
+  return __byte_perm(w, 0u, 0x4440u | (uint32_t)i);
+#else
+  return (w >> (8 * i)) & 0xFFu;
 #endif
 }
 
@@ -264,10 +290,9 @@ RT_HD uint32_t wide_node_test(const float4 n0, const uint4 n1, const uint4 n2, c
             tfz = fmaf(byte2f_biased(fz, j), afz, bfz);
       float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
       float tf = fminf(fminf(tfx, tfy), fminf(tfz, tmax));
-      if (tn <= tf) {
-        uint32_t cb = (child_bits4 >> (8 * j)) & 0xFFu, bi = (bit_index4 >> (8 * j)) & 0xFFu;
-        hitmask |= cb << bi;
-      }
+      // branch-free: the (cheap) bit placement is done for every child and masked by the test
+      const uint32_t cb = byte_of(child_bits4, j), bi = byte_of(bit_index4, j);
+      hitmask |= (tn <= tf) ? (cb << bi) : 0u;
     }
   }
   return hitmask;

@@ -54,7 +54,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--accel", type=int, default=0, help="0 = compressed 8-wide BVH (product), 1 = binary LBVH cross-check")
+    ap.add_argument("--accel", type=int, default=0, help="RT_ACCEL_*: 0 = default (binary BVH), 3 = compressed 8-wide BVH")
     ap.add_argument("--sky", type=int, default=2048, help="procedural skybox face size")
     return ap.parse_args()
 
@@ -148,7 +148,8 @@ def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix):
     n_shadow = st_count["rays_shadow"]
     node_b, tri_b = st_count["node_bytes"], st_count["tri_bytes"]
     trav_bytes = n_node * node_b + n_tri * tri_b + n_closest * (32 + 16 + 4) + n_shadow * (48 + 16)
-    trav_flops = n_node * 8 * 24 + n_tri * 50
+    children = 8 if node_b == 80 else 2      # boxes tested per node visit of the active layout
+    trav_flops = n_node * children * 24 + n_tri * 50
     achieved = trav_bytes / (trav_ms * 1e-3) / 1e9
     frame_bytes = (trav_bytes + st_count["n_hit"] * 84 + st_count["n_miss"] * 16 + n_closest * 32 + npix * 4)
     frame_flops = trav_flops + st_count["n_hit"] * 120
@@ -165,7 +166,7 @@ def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix):
         "achieved": round(achieved, 1), "peak": hbm_gbs, "peak_source": hbm_src, "unit": "GB/s",
         "frac": round(achieved / hbm_gbs, 4), "traffic": traffic,
         "algorithmic_bytes_per_frame": int(trav_bytes), "traversal_ms": round(trav_ms, 4),
-        "nodes_visited": int(n_node), "tris_tested": int(n_tri), "node_bytes": node_b, "tri_bytes": tri_b,
+        "nodes_visited": int(n_node), "tris_tested": int(n_tri), "node_bytes": node_b, "tri_bytes": tri_b, "boxes_per_node": children,
         "flop_term": {"flops_per_frame": int(trav_flops), "achieved_tflops": round(trav_flops / (trav_ms * 1e-3) / 1e12, 3),
                       "fp32_peak_tflops_measured": round(fp32_tflops, 2),
                       "frac": round(trav_flops / (trav_ms * 1e-3) / 1e12 / fp32_tflops, 4) if fp32_tflops else None},

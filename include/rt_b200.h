@@ -46,14 +46,22 @@ enum { RT_TYPE_DIFFUSE = 0, RT_TYPE_MIRROR = 1, RT_TYPE_REFRACTIVE = 2 };
 enum { RT_FORMAT_RGBA8 = 0, RT_FORMAT_RGBA32F = 1 };
 enum { RT_LOCATION_HOST = 0, RT_LOCATION_DEVICE = 1 };
 
-/* Acceleration-structure flavours (rt_scene_desc.flags, low 4 bits). */
+/* Acceleration-structure flavours (rt_scene_desc.flags, low 4 bits).  Every flavour is built
+ * from the same LBVH (Morton sort -> Karras tree -> SAH treelet refinement); they differ in
+ * the node layout the traversal kernels read. */
 enum {
-  RT_ACCEL_DEFAULT = 0,   /* compressed 8-wide BVH (the product path)           */
-  RT_ACCEL_BVH2 = 1,      /* plain Karras LBVH, binary traversal (cross-check)   */
-  RT_ACCEL_BRUTE = 2      /* no hierarchy: every ray tests every triangle (tiny
-                             scenes only; parity cross-check)                    */
+  RT_ACCEL_DEFAULT = 0,   /* the product path: currently RT_ACCEL_BVH2 (fastest measured on
+                             B200)                                   */
+  RT_ACCEL_BVH2 = 1,      /* binary nodes, two FP32 child boxes, 64 B = 2 x 256-bit loads;
+                             ordered traversal                                            */
+  RT_ACCEL_BRUTE = 2,     /* no hierarchy: every ray tests every triangle (tiny scenes
+                             only; parity cross-check)                                    */
+  RT_ACCEL_WIDE8 = 3      /* compressed 8-wide nodes (80 B, 8-bit quantised child boxes,
+                             Ylitie et al. 2017): least memory traffic per ray            */
 };
 #define RT_FLAG_ACCEL_MASK 0xFu
+/* Skip the SAH treelet refinement of the Karras tree (faster build, slower rays). */
+#define RT_FLAG_NO_REFINE 0x10u
 
 /* One triangle mesh = one bottom-level acceleration structure.
  * Replaces createBLASGeometry/createBLAS/buildBLAS (main.cpp:305-536) and the
@@ -92,7 +100,7 @@ typedef struct rt_scene_desc {
   const uint8_t* skybox_rgba8;
   uint32_t sky_w, sky_h;
   int32_t device_id;      /* CUDA ordinal; -1 = current device */
-  uint32_t flags;         /* RT_ACCEL_* */
+  uint32_t flags;         /* RT_ACCEL_* | RT_FLAG_* */
 } rt_scene_desc;
 
 /* Camera vectors exactly as they reach the uniform block (main.cpp:1848-1851,

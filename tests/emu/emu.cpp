@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <numeric>
@@ -113,6 +114,13 @@ void build(EmuBlas& b, uint32_t accel) {
     a.keys = keys.data();
     for (uint32_t i = 0; i + 1 < N; i++) karras_node(a, (int)i);
     for (uint32_t j = 0; j < N; j++) refit_from_leaf(a, j);
+    const int treelet_passes = getenv("RT_TREELET_PASSES") ? atoi(getenv("RT_TREELET_PASSES")) : 2;
+    std::vector<float> cost(2 * (size_t)N);
+    a.cost = cost.data();
+    for (int pass = 0; pass < treelet_passes && N > 2; pass++) {
+      std::fill(flags.begin(), flags.end(), 0u);
+      for (uint32_t j = 0; j < N; j++) treelet_from_leaf(a, j);
+    }
     if (accel == ACCEL_WIDE) {
       b.wide.resize(5 * (size_t)N);
       a.wide = b.wide.data();
@@ -167,7 +175,10 @@ extern "C" {
 
 int emu_scene_create(const rt_scene_desc* d, void** out) {
   auto s = std::make_unique<EmuScene>();
-  s->accel = d->flags & RT_FLAG_ACCEL_MASK;
+  {  // same API flavour -> traversal id mapping as rt_scene_build()
+    const uint32_t f = d->flags & RT_FLAG_ACCEL_MASK;
+    s->accel = f == RT_ACCEL_WIDE8 ? (uint32_t)ACCEL_WIDE : (f == RT_ACCEL_BRUTE ? (uint32_t)ACCEL_BRUTE : (uint32_t)ACCEL_BVH2);
+  }
   s->blas.resize(d->n_meshes);
   for (uint32_t i = 0; i < d->n_meshes; i++) {
     s->blas[i].verts.assign(d->meshes[i].vertices, d->meshes[i].vertices + 6 * (size_t)d->meshes[i].n_vertices);
@@ -190,6 +201,7 @@ int emu_scene_create(const rt_scene_desc* d, void** out) {
 void emu_scene_destroy(void* s) { delete (EmuScene*)s; }
 uint64_t emu_bvh_nodes(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].nodes; }
 const void* emu_wide_nodes(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].wide.data(); }
+const void* emu_bvh2_nodes(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].bvh2.data(); }
 const void* emu_leaf_tris(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].tris.data(); }
 
 // same outputs as orc_render; counts[6..7] = nodes visited, tris tested

@@ -22,6 +22,8 @@ def lib():
         L.emu_bvh_nodes.argtypes = [C.c_void_p, C.c_uint32]
         L.emu_wide_nodes.restype = C.c_void_p
         L.emu_wide_nodes.argtypes = [C.c_void_p, C.c_uint32]
+        L.emu_bvh2_nodes.restype = C.c_void_p
+        L.emu_bvh2_nodes.argtypes = [C.c_void_p, C.c_uint32]
         L.emu_leaf_tris.restype = C.c_void_p
         L.emu_leaf_tris.argtypes = [C.c_void_p, C.c_uint32]
         L.emu_slot_to_pixel.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
@@ -66,6 +68,12 @@ class EmuScene:
         n = int(lib().emu_bvh_nodes(self._h, mesh))
         p = lib().emu_wide_nodes(self._h, mesh)
         return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint32)), (n, 20)).copy()
+
+    def bvh2_nodes(self, mesh=0):
+        """(n, 16) float32 view of the binary nodes: child boxes + child ids (as int bits)."""
+        n = int(lib().emu_bvh_nodes(self._h, mesh))
+        p = lib().emu_bvh2_nodes(self._h, mesh)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), (n, 16)).copy()
 
     def leaf_tris(self, mesh, ntri):
         p = lib().emu_leaf_tris(self._h, mesh)

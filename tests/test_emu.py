@@ -20,7 +20,7 @@ def compare(rt, ob, emu, inputs, params, accel, cam=None):
     return a["counts"]
 
 
-@pytest.mark.parametrize("accel", [0, 1, 2])
+@pytest.mark.parametrize("accel", [0, 2, 3])
 def test_smoke_scene_bit_exact(rt, ob, emu, accel):
     compare(rt, ob, emu, scenes.smoke_scene(rt), rt.FrameParams.make(96, 72, 6, 3), accel)
 
@@ -44,7 +44,7 @@ def test_tiny_and_degenerate_meshes(rt, ob, emu):
     cv, ci = scenes.unit_cube()
     one = (np.array([[-3, -3, 0, 0, 0, 1], [3, -3, 0, 0, 0, 1], [0, 3, 0, 0, 0, 1]], np.float32),
            np.array([[0, 1, 2]], np.uint32))
-    for accel in (0, 1, 2):
+    for accel in (0, 2, 3):
         compare(rt, ob, emu, rt.SceneInputs([one], [(0, 0, rt.IDENTITY34)], None), rt.FrameParams.make(40, 30, 0, 1), accel)
     two = (cv, ci[:2])
     dup = (np.concatenate([cv, cv[:3]]), np.concatenate([ci, ci[:4], np.array([[0, 0, 1], [2, 2, 2]], np.uint32)]))
@@ -52,7 +52,7 @@ def test_tiny_and_degenerate_meshes(rt, ob, emu):
     inputs = rt.SceneInputs([two, dup, empty], [(0, 1, rt.translation34(-3, 0, 0)), (1, 2, rt.IDENTITY34),
                                                 (2, 0, rt.IDENTITY34), (1, 7, rt.translation34(3, 0, 2))],
                             scenes.sea_sky_64())
-    for accel in (0, 1):
+    for accel in (0, 3):
         compare(rt, ob, emu, inputs, rt.FrameParams.make(80, 60, 4, 2), accel)
 
 
@@ -88,7 +88,7 @@ def test_wide_bvh_structure(rt, emu):
     """Every triangle sits in exactly one leaf, every node is referenced exactly once, and each
     quantised child box contains the geometry below it."""
     v, i = rt.make_standin_armadillo(3)
-    es = emu.EmuScene(rt.SceneInputs([(v, i)], [(0, 0, rt.IDENTITY34)], None), 0)
+    es = emu.EmuScene(rt.SceneInputs([(v, i)], [(0, 0, rt.IDENTITY34)], None), rt.ACCEL_WIDE8)
     nodes = es.wide_nodes(0)
     tris = es.leaf_tris(0, i.shape[0])
     prims = tris[:, 3].copy().view(np.uint32)
@@ -119,6 +119,56 @@ def test_wide_bvh_structure(rt, emu):
 
     bounds(0)
     assert len(seen_nodes) == nodes.shape[0] and len(seen_tris) == i.shape[0]
+
+
+@pytest.mark.parametrize("passes", ["0", "2"])
+def test_binary_bvh_structure(rt, emu, passes, monkeypatch):
+    """After the SAH treelet refinement the binary tree is still a tree: every node is reached
+    exactly once from the root, every triangle sits in exactly one leaf and every child box
+    contains the geometry below it.  Refinement must lower the SAH cost."""
+    monkeypatch.setenv("RT_TREELET_PASSES", passes)
+    v, i = rt.make_standin_armadillo(3)
+    es = emu.EmuScene(rt.SceneInputs([(v, i)], [(0, 0, rt.IDENTITY34)], None), rt.ACCEL_BVH2)
+    nodes = es.bvh2_nodes(0)
+    ntri = i.shape[0]
+    assert nodes.shape[0] == ntri - 1
+    tris = es.leaf_tris(0, ntri)
+    prims = tris[:, 3].copy().view(np.uint32)
+    assert sorted(prims.tolist()) == list(range(ntri))
+    child = nodes[:, 12:14].copy().view(np.int32)
+    seen_nodes, seen_leaves = {0}, set()
+    area = [0.0]
+
+    def bounds(n):
+        lo, hi = np.full(3, np.inf), np.full(3, -np.inf)
+        boxes = [(nodes[n, 0:3], nodes[n, 3:6]), (nodes[n, 6:9], nodes[n, 9:12])]
+        for c, (clo, chi) in zip(child[n], boxes):
+            if c >= 0:
+                assert c not in seen_nodes
+                seen_nodes.add(int(c))
+                blo, bhi = bounds(int(c))
+            else:
+                slot = ~int(c)
+                assert slot not in seen_leaves
+                seen_leaves.add(slot)
+                pts = tris[slot][[0, 1, 2, 4, 5, 6, 8, 9, 10]].reshape(3, 3)
+                blo, bhi = pts.min(0), pts.max(0)
+            assert np.all(clo <= blo + 1e-9) and np.all(chi >= bhi - 1e-9), "child box does not contain its geometry"
+            d = chi - clo
+            area[0] += float(d[0] * d[1] + d[1] * d[2] + d[2] * d[0])
+            lo, hi = np.minimum(lo, clo), np.maximum(hi, chi)
+        return lo, hi
+
+    import sys
+    sys.setrecursionlimit(10000)
+    bounds(0)
+    assert len(seen_nodes) == ntri - 1 and len(seen_leaves) == ntri
+    test_binary_bvh_structure.area[passes] = area[0]
+    if len(test_binary_bvh_structure.area) == 2:
+        assert test_binary_bvh_structure.area["2"] < 0.97 * test_binary_bvh_structure.area["0"]
+
+
+test_binary_bvh_structure.area = {}
 
 
 def test_trace_rays_matches_oracle_brute_force(rt, ob, emu):

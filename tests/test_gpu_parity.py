@@ -43,7 +43,7 @@ def check_frame(rt, ob, inputs, params, accel=0, cam=None, exact=True):
     return st
 
 
-@pytest.mark.parametrize("accel", [0, 1, 2])
+@pytest.mark.parametrize("accel", [0, 2, 3])
 def test_smoke_scene_all_accels(gpu_rt, ob, accel):
     check_frame(gpu_rt, ob, scenes.smoke_scene(gpu_rt), gpu_rt.FrameParams.make(160, 120, 6, 4), accel)
 

@@ -30,7 +30,8 @@ HOST_LIB_PATH = os.path.join(_HERE, "librt_host.so")
 TYPE_DIFFUSE, TYPE_MIRROR, TYPE_REFRACTIVE = 0, 1, 2
 FORMAT_RGBA8, FORMAT_RGBA32F = 0, 1
 LOCATION_HOST, LOCATION_DEVICE = 0, 1
-ACCEL_DEFAULT, ACCEL_BVH2, ACCEL_BRUTE = 0, 1, 2
+ACCEL_DEFAULT, ACCEL_BVH2, ACCEL_BRUTE, ACCEL_WIDE8 = 0, 1, 2, 3
+FLAG_NO_REFINE = 0x10
 MISS = 0xFFFFFFFF
 
 

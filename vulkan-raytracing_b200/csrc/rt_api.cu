@@ -15,7 +15,7 @@ thread_local std::string g_err;
 struct Scene {
   int device = 0;
   cudaStream_t stream = nullptr;
-  uint32_t accel = ACCEL_WIDE;
+  uint32_t accel = ACCEL_BVH2;
   std::vector<BlasHost> blas;
   std::vector<InstDev> inst;
   BlasDev* d_blas = nullptr;
@@ -159,8 +159,12 @@ int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
   if (!d || !out_scene) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
   *out_scene = nullptr;
   if (d->n_meshes == 0 || !d->meshes || (d->n_instances && !d->instances)) return fail(RT_ERR_INVALID_ARGUMENT, "empty scene");
-  const uint32_t accel = d->flags & RT_FLAG_ACCEL_MASK;
-  if (accel > RT_ACCEL_BRUTE) return fail(RT_ERR_INVALID_ARGUMENT, "unknown accel flag");
+  const uint32_t accel_flag = d->flags & RT_FLAG_ACCEL_MASK;
+  if (accel_flag > RT_ACCEL_WIDE8) return fail(RT_ERR_INVALID_ARGUMENT, "unknown accel flag");
+  // API flavour -> internal traversal id (template parameter of the kernels)
+  const uint32_t accel = accel_flag == RT_ACCEL_WIDE8 ? (uint32_t)ACCEL_WIDE
+                         : accel_flag == RT_ACCEL_BRUTE ? (uint32_t)ACCEL_BRUTE : (uint32_t)ACCEL_BVH2;
+  const bool refine = (d->flags & RT_FLAG_NO_REFINE) == 0;
   for (uint32_t i = 0; i < d->n_meshes; i++) {
     const rt_mesh_desc& m = d->meshes[i];
     if ((m.n_triangles && (!m.indices || !m.vertices)) || (m.n_vertices && !m.vertices)) return fail(RT_ERR_INVALID_ARGUMENT, "null mesh buffer");
@@ -197,7 +201,7 @@ int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
   }
   RT_CUDA_TRY(cudaEventRecord(e0, s->stream), g_err);
   for (uint32_t i = 0; i < d->n_meshes; i++) {
-    int rc = build_blas(s->blas[i], d->meshes[i].n_vertices, d->meshes[i].n_triangles, (int)accel, s->stream, g_err);
+    int rc = build_blas(s->blas[i], d->meshes[i].n_vertices, d->meshes[i].n_triangles, (int)accel, refine, s->stream, g_err);
     if (rc != RT_OK) return rc;
   }
   RT_CUDA_TRY(cudaEventRecord(e1, s->stream), g_err);

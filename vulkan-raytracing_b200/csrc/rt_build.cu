@@ -7,6 +7,7 @@
 // 8 x 8 B r, tree arrays ~40 B, box fit ~96 B, wide emit 48 B (triangle) + ~25 B (node).
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 
 #include "rt_build.cuh"
 #include "rt_internal.h"
@@ -260,6 +261,12 @@ __global__ void __launch_bounds__(256) k_refit(BuildArrays a) {
     refit_from_leaf(a, j);
 }
 
+// one SAH treelet-refinement pass (rt_build.cuh): thread j climbs from sorted leaf j
+__global__ void __launch_bounds__(128) k_treelet(BuildArrays a) {
+  for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < a.ntri; j += gridDim.x * blockDim.x)
+    treelet_from_leaf(a, j);
+}
+
 __global__ void __launch_bounds__(128) k_collapse(BuildArrays a, uint32_t begin, uint32_t end) {
   for (uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x; w < end; w += gridDim.x * blockDim.x)
     collapse_node(a, w);
@@ -305,7 +312,7 @@ void free_blas(BlasHost& b) {
   b = BlasHost{};
 }
 
-int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, cudaStream_t stream, std::string& err) {
+int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refine, cudaStream_t stream, std::string& err) {
   b.dev.verts = b.d_verts;
   b.dev.idx = b.d_idx;
   b.dev.ntri = ntri;
@@ -349,6 +356,14 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, cudaStream
     if (rc != RT_OK) return rc;
     if (ntri > 1) k_karras<<<grid_for(N, 256), 256, 0, stream>>>(a);
     k_refit<<<grid_for(N, 256), 256, 0, stream>>>(a);
+    static const int treelet_passes = getenv("RT_TREELET_PASSES") ? atoi(getenv("RT_TREELET_PASSES")) : 2;
+    if (ntri > 2 && refine && treelet_passes > 0) {
+      RT_CUDA_TRY(tmp.get(&a.cost, 2 * N), err);
+      for (int pass = 0; pass < treelet_passes; pass++) {
+        RT_CUDA_TRY(cudaMemsetAsync(a.flags, 0, N * sizeof(uint32_t), stream), err);
+        k_treelet<<<grid_for(N, 128), 128, 0, stream>>>(a);
+      }
+    }
   }
   RT_CUDA_TRY(cudaGetLastError(), err);
 

@@ -44,7 +44,8 @@ struct BuildArrays {
   uint32_t* first;        // [ntri-1] first leaf covered
   float4* node_lo;        // [2*ntri-1] xyz = box min, w = leaf count (as uint bits)
   float4* node_hi;        // [2*ntri-1]
-  uint32_t* flags;        // [ntri-1] arrival counters of the bottom-up pass
+  uint32_t* flags;        // [ntri-1] arrival counters of the bottom-up passes
+  float* cost;            // [2*ntri-1] SAH cost of the subtree (treelet refinement)
   // wide output
   uint4* wide;            // 5 x uint4 per node
   float4* tris;           // 3 x float4 per leaf triangle
@@ -162,6 +163,135 @@ RT_HD void refit_from_leaf(const BuildArrays& a, uint32_t j) {
 RT_HD float half_area(float4 lo, float4 hi) {
   const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
   return dx * dy + dy * dz + dz * dx;
+}
+
+// ---- SAH treelet refinement (Karras & Aila 2013, "Fast parallel construction of high-quality
+// bounding volume hierarchies", section 3) ------------------------------------------------------
+// The Karras tree follows the Morton curve, not the surface area heuristic.  Bottom-up, every
+// inner node becomes the root of a treelet: itself plus the (up to) 5 descendants reached by
+// repeatedly opening the treelet leaf with the largest area, i.e. 7 treelet leaves.  Dynamic
+// programming over the 2^7 leaf subsets finds the topology with the smallest SAH cost
+//   C(s) = CT * area(s) + min over splits p of C(p) + C(s \ p),   C({leaf}) = subtree cost,
+// and the treelet's inner nodes are rewritten in place (same node ids, root keeps its id, so the
+// parent above is untouched).  One thread per treelet; threads climb from the leaves with the
+// same second-arrival rule as the box fit, so a treelet is only touched after everything below
+// it is final.  Subtrees no longer cover contiguous Morton ranges afterwards.
+static const int TREELET_LEAVES = 7;
+#define RT_SAH_CT 1.0f   // cost of one inner node visit (two box tests)
+#define RT_SAH_CI 1.3f   // cost of one triangle test
+
+RT_HD void treelet_optimize_node(const BuildArrays& a, int x) {
+  const int n = (int)a.ntri;
+  int leaves[TREELET_LEAVES], inner[TREELET_LEAVES - 1];
+  float4 llo[TREELET_LEAVES], lhi[TREELET_LEAVES];
+  int nl = 0, ni = 0;
+  inner[ni++] = x;
+  leaves[0] = RT_LDCG(&a.left[x]);
+  leaves[1] = RT_LDCG(&a.right[x]);
+  nl = 2;
+  for (int i = 0; i < 2; i++) { llo[i] = RT_LDCG(&a.node_lo[leaves[i]]); lhi[i] = RT_LDCG(&a.node_hi[leaves[i]]); }
+  float inner_area = half_area(RT_LDCG(&a.node_lo[x]), RT_LDCG(&a.node_hi[x]));  // sum over the treelet's inner nodes
+  while (nl < TREELET_LEAVES) {
+    int best = -1;
+    float ba = -1.0f;
+    for (int i = 0; i < nl; i++) {
+      if (leaves[i] >= n - 1) continue;
+      const float ar = half_area(llo[i], lhi[i]);
+      if (ar > ba) { ba = ar; best = i; }
+    }
+    if (best < 0) break;
+    const int id = leaves[best];
+    inner[ni++] = id;
+    inner_area += ba;
+    leaves[best] = RT_LDCG(&a.left[id]);
+    leaves[nl] = RT_LDCG(&a.right[id]);
+    llo[best] = RT_LDCG(&a.node_lo[leaves[best]]); lhi[best] = RT_LDCG(&a.node_hi[leaves[best]]);
+    llo[nl] = RT_LDCG(&a.node_lo[leaves[nl]]); lhi[nl] = RT_LDCG(&a.node_hi[leaves[nl]]);
+    nl++;
+  }
+  float lcost[TREELET_LEAVES];
+  float cur = RT_SAH_CT * inner_area;
+  for (int i = 0; i < nl; i++) { lcost[i] = RT_LDCG(&a.cost[leaves[i]]); cur += lcost[i]; }
+  if (nl < 3) { a.cost[x] = cur; return; }  // two leaves: nothing to rearrange
+  const int S = 1 << nl;
+  float area[1 << TREELET_LEAVES], copt[1 << TREELET_LEAVES];
+  uint8_t part[1 << TREELET_LEAVES];
+  for (int s = 1; s < S; s++) {
+    float lx = 3.0e38f, ly = 3.0e38f, lz = 3.0e38f, hx = -3.0e38f, hy = -3.0e38f, hz = -3.0e38f;
+    for (int i = 0; i < nl; i++)
+      if (s & (1 << i)) {
+        lx = fminf(lx, llo[i].x); ly = fminf(ly, llo[i].y); lz = fminf(lz, llo[i].z);
+        hx = fmaxf(hx, lhi[i].x); hy = fmaxf(hy, lhi[i].y); hz = fmaxf(hz, lhi[i].z);
+      }
+    const float dx = hx - lx, dy = hy - ly, dz = hz - lz;
+    area[s] = dx * dy + dy * dz + dz * dx;
+  }
+  for (int i = 0; i < nl; i++) copt[1 << i] = lcost[i];
+  for (int sz = 2; sz <= nl; sz++)
+    for (int s = 3; s < S; s++) {
+      if (popc32((uint32_t)s) != sz) continue;
+      float bc = 3.0e38f;
+      int bp = 0;
+      const int delta = (s - 1) & s;  // s without its lowest bit: enumerate each split once
+      int p = (-delta) & s;
+      do {
+        const float c = copt[p] + copt[s ^ p];
+        if (c < bc) { bc = c; bp = p; }
+        p = (p - delta) & s;
+      } while (p != 0);
+      copt[s] = RT_SAH_CT * area[s] + bc;
+      part[s] = (uint8_t)bp;
+    }
+  if (!(copt[S - 1] < cur * 0.9999f)) { a.cost[x] = cur; return; }
+  // rewrite the treelet: breadth-first over the chosen splits, ids taken from inner[]
+  int qs[TREELET_LEAVES], qid[TREELET_LEAVES];
+  int qh = 0, qt = 0, next = 1;
+  qs[qt] = S - 1; qid[qt] = x; qt++;
+  while (qh < qt) {
+    const int s = qs[qh], id = qid[qh];
+    qh++;
+    const int sub[2] = {(int)part[s], s ^ (int)part[s]};
+    int ch[2];
+    for (int c = 0; c < 2; c++) {
+      if ((sub[c] & (sub[c] - 1)) == 0) {
+        ch[c] = leaves[bfind32((uint32_t)sub[c])];
+      } else {
+        ch[c] = inner[next++];
+        qs[qt] = sub[c]; qid[qt] = ch[c]; qt++;
+      }
+    }
+    float lx = 3.0e38f, ly = 3.0e38f, lz = 3.0e38f, hx = -3.0e38f, hy = -3.0e38f, hz = -3.0e38f;
+    uint32_t cnt = 0;
+    for (int i = 0; i < nl; i++)
+      if (s & (1 << i)) {
+        lx = fminf(lx, llo[i].x); ly = fminf(ly, llo[i].y); lz = fminf(lz, llo[i].z);
+        hx = fmaxf(hx, lhi[i].x); hy = fmaxf(hy, lhi[i].y); hz = fmaxf(hz, lhi[i].z);
+        cnt += f2u(llo[i].w);
+      }
+    a.left[id] = ch[0];
+    a.right[id] = ch[1];
+    a.parent[ch[0]] = id;
+    a.parent[ch[1]] = id;
+    a.node_lo[id] = make_float4(lx, ly, lz, u2f(cnt));
+    a.node_hi[id] = make_float4(hx, hy, hz, 0.0f);
+    a.cost[id] = copt[s];
+  }
+}
+
+// bottom-up driver of one refinement pass, started once per leaf j (sorted position)
+RT_HD void treelet_from_leaf(const BuildArrays& a, uint32_t j) {
+  const int n = (int)a.ntri;
+  const int leaf = (n - 1) + (int)j;
+  a.cost[leaf] = RT_SAH_CI * half_area(a.node_lo[leaf], a.node_hi[leaf]);
+  if (n == 1) return;
+  int node = a.parent[leaf];
+  while (true) {
+    RT_FENCE();
+    if (RT_ATOMIC_ADD(&a.flags[node], 1u) == 0u) return;
+    treelet_optimize_node(a, node);
+    if (node == 0) return;
+    node = RT_LDCG(&a.parent[node]);
+  }
 }
 
 static const uint32_t WIDE_LEAF_MAX = 3;   // triangles per leaf child (unary count in 3 bits)

@@ -31,7 +31,7 @@ struct BlasHost {
 };
 
 // Builds the acceleration structure of one mesh already resident on the device.
-int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, cudaStream_t stream, std::string& err);
+int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refine, cudaStream_t stream, std::string& err);
 void free_blas(BlasHost& b);
 
 // LSD radix sort of (key,value) pairs, 8 bits per pass over `key_bits` bits; result in

@@ -752,7 +752,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     launches += 4;
     last_bounce = j;
     if (j < U.max_bounce) {
-      const bool sorting = accel == ACCEL_WIDE && (int)(j + 1) >= sort_from;
+      const bool sorting = accel != ACCEL_BRUTE && (int)(j + 1) >= sort_from;
       k_shade_spec<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, cn, p->qSpec, p->rayO[cur], p->rayD[cur], p->hits,
                                                    p->rayO[cur ^ 1], p->rayD[cur ^ 1], sorting ? p->sortK[0] : nullptr,
                                                    sorting ? p->sortV[0] : nullptr);

@@ -176,8 +176,8 @@ RT_HD void slab_interval(const RayObj& r, float lox, float loy, float loz, float
   const float t1z = (loz - r.o.z) * r.idir.z, t2z = (hiz - r.o.z) * r.idir.z;
   const float n = fmaxf(fmaxf(fminf(t1x, t2x), fminf(t1y, t2y)), fminf(t1z, t2z));
   const float f = fminf(fminf(fmaxf(t1x, t2x), fmaxf(t1y, t2y)), fmaxf(t1z, t2z));
-  tn = fmaxf(n * 0.99999f, tmin);
-  tf = fminf(f * 1.00001f, tmax);
+  tn = fmaxf(fmaf(-1e-5f, fabsf(n), n), tmin);   // sign-aware: also right for intervals behind the origin
+  tf = fminf(fmaf(1e-5f, fabsf(f), f), tmax);
 }
 
 template <class Stack, bool ANY, bool COUNT>
@@ -365,7 +365,7 @@ RT_HD bool trace_scene(const SceneDev& s, f3 o, f3 d, float tmin, float tmax, Hi
       if (!slab_test(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], tmin, best.t)) continue;
     }
     const RayObj r = ray_setup(xform_point(in.w2o, o), xform_vector(in.w2o, d));
-    const BlasDev& b = s.blas[in.mesh];
+    const BlasDev b = s.blas[in.mesh];  // by value: the node / triangle base pointers stay in registers
     bool hit;
     if (s.accel == ACCEL_WIDE) hit = trace_wide<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
     else if (s.accel == ACCEL_BVH2) hit = trace_bvh2<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);

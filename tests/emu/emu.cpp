@@ -114,7 +114,7 @@ void build(EmuBlas& b, uint32_t accel) {
     a.keys = keys.data();
     for (uint32_t i = 0; i + 1 < N; i++) karras_node(a, (int)i);
     for (uint32_t j = 0; j < N; j++) refit_from_leaf(a, j);
-    const int treelet_passes = getenv("RT_TREELET_PASSES") ? atoi(getenv("RT_TREELET_PASSES")) : 2;
+    const int treelet_passes = getenv("RT_TREELET_PASSES") ? atoi(getenv("RT_TREELET_PASSES")) : 1;
     std::vector<float> cost(2 * (size_t)N);
     a.cost = cost.data();
     for (int pass = 0; pass < treelet_passes && N > 2; pass++) {

@@ -26,158 +26,6 @@ int sm_count() {
 }
 
 // ------------------------------------------------------------------------------------------
-// radix sort: 8-bit digits, per pass: tile histograms -> per-digit scan over tiles -> stable
-// scatter (warp match ranking).  Tile = 256 threads x 16 keys.
-// ------------------------------------------------------------------------------------------
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
-
-size_t sort_hist_words(uint64_t n) { return 256 * ((n + SORT_TILE - 1) / SORT_TILE) + 256; }
-
-__global__ void __launch_bounds__(SORT_THREADS) k_sort_hist(const uint64_t* __restrict__ keys, uint64_t n, int shift,
-                                                            uint32_t* __restrict__ hist, uint32_t num_tiles) {
-  __shared__ uint32_t sh[256];
-  const uint32_t tile = blockIdx.x;
-  sh[threadIdx.x] = 0;
-  __syncthreads();
-  const uint64_t base = (uint64_t)tile * SORT_TILE;
-#pragma unroll 4
-  for (int r = 0; r < SORT_ITEMS; r++) {
-    const uint64_t p = base + (uint64_t)r * SORT_THREADS + threadIdx.x;
-    if (p < n) atomicAdd(&sh[(uint32_t)(keys[p] >> shift) & 0xFFu], 1u);
-  }
-  __syncthreads();
-  hist[(size_t)threadIdx.x * num_tiles + tile] = sh[threadIdx.x];
-}
-
-// one block per digit: exclusive scan of that digit's counts over all tiles
-__global__ void __launch_bounds__(256) k_sort_scan(uint32_t* __restrict__ hist, uint32_t num_tiles,
-                                                   uint32_t* __restrict__ totals) {
-  __shared__ uint32_t warp_sum[8];
-  __shared__ uint32_t carry_s;
-  uint32_t* row = hist + (size_t)blockIdx.x * num_tiles;
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry_s = 0;
-  __syncthreads();
-  for (uint32_t base = 0; base < num_tiles; base += 256) {
-    const uint32_t i = base + threadIdx.x;
-    const uint32_t v = i < num_tiles ? row[i] : 0u;
-    uint32_t x = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
-      if (lane >= o) x += y;
-    }
-    if (lane == 31) warp_sum[wid] = x;
-    __syncthreads();
-    uint32_t wbase = 0;
-    for (int w = 0; w < wid; w++) wbase += warp_sum[w];
-    const uint32_t carry = carry_s;
-    if (i < num_tiles) row[i] = carry + wbase + x - v;
-    __syncthreads();
-    if (threadIdx.x == 255) carry_s = carry + wbase + x;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) totals[blockIdx.x] = carry_s;
-}
-
-__global__ void __launch_bounds__(SORT_THREADS)
-    k_sort_scatter(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout,
-                   uint32_t* __restrict__ vout, uint64_t n, int shift, const uint32_t* __restrict__ hist,
-                   const uint32_t* __restrict__ totals, uint32_t num_tiles) {
-  __shared__ uint32_t warp_cnt[SORT_THREADS / 32][256];
-  __shared__ uint32_t digit_base[256];
-  __shared__ uint32_t wsum[8];
-  const uint32_t tile = blockIdx.x;
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  // exclusive scan of the 256 digit totals -> global start of each digit
-  {
-    const uint32_t v = totals[threadIdx.x];
-    uint32_t x = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
-      if (lane >= o) x += y;
-    }
-    if (lane == 31) wsum[wid] = x;
-    for (int w = 0; w < SORT_THREADS / 32; w++) warp_cnt[w][threadIdx.x] = 0;
-    __syncthreads();
-    uint32_t wb = 0;
-    for (int w = 0; w < wid; w++) wb += wsum[w];
-    digit_base[threadIdx.x] = wb + x - v + hist[(size_t)threadIdx.x * num_tiles + tile];
-  }
-  __syncthreads();
-  uint64_t key[SORT_ITEMS];
-  uint32_t val[SORT_ITEMS];
-  uint32_t rank[SORT_ITEMS];
-  const uint64_t base = (uint64_t)tile * SORT_TILE + (uint64_t)wid * (SORT_ITEMS * 32) + lane;
-  const uint32_t lt_mask = (1u << lane) - 1u;
-#pragma unroll
-  for (int r = 0; r < SORT_ITEMS; r++) {
-    const uint64_t p = base + (uint64_t)r * 32;
-    const bool valid = p < n;
-    key[r] = valid ? kin[p] : 0ull;
-    val[r] = valid ? vin[p] : 0u;
-  }
-#pragma unroll
-  for (int r = 0; r < SORT_ITEMS; r++) {
-    const uint64_t p = base + (uint64_t)r * 32;
-    const bool valid = p < n;
-    const uint32_t d = valid ? ((uint32_t)(key[r] >> shift) & 0xFFu) : 0x100u;
-    const uint32_t peers = __match_any_sync(0xFFFFFFFFu, d);
-    const uint32_t prior = valid ? warp_cnt[wid][d] : 0u;
-    __syncwarp();
-    const uint32_t before = __popc(peers & lt_mask);
-    if (valid && before == 0) warp_cnt[wid][d] = prior + __popc(peers);
-    __syncwarp();
-    rank[r] = prior + before;
-  }
-  __syncthreads();
-  {  // exclusive scan over warps, per digit
-    uint32_t run = 0;
-    for (int w = 0; w < SORT_THREADS / 32; w++) {
-      const uint32_t c = warp_cnt[w][threadIdx.x];
-      warp_cnt[w][threadIdx.x] = run;
-      run += c;
-    }
-  }
-  __syncthreads();
-#pragma unroll
-  for (int r = 0; r < SORT_ITEMS; r++) {
-    const uint64_t p = base + (uint64_t)r * 32;
-    if (p < n) {
-      const uint32_t d = (uint32_t)(key[r] >> shift) & 0xFFu;
-      const uint32_t dst = digit_base[d] + warp_cnt[wid][d] + rank[r];
-      kout[dst] = key[r];
-      vout[dst] = val[r];
-    }
-  }
-}
-
-int sort_pairs(uint64_t* keys, uint64_t* keys_alt, uint32_t* vals, uint32_t* vals_alt, uint64_t n, int key_bits,
-               uint32_t* hist, cudaStream_t stream, std::string& err) {
-  if (n == 0) return RT_OK;
-  if (n > 0xFFFFFFFFull) { err = "sort_pairs: n exceeds 32-bit positions"; return RT_ERR_UNSUPPORTED; }
-  const uint32_t num_tiles = (uint32_t)((n + SORT_TILE - 1) / SORT_TILE);
-  int passes = (key_bits + 7) / 8;
-  if (passes & 1) passes++;  // even number of passes: the result lands in keys/vals
-  uint32_t* totals = hist + (size_t)256 * num_tiles;
-  uint64_t* kin = keys; uint64_t* kout = keys_alt;
-  uint32_t* vin = vals; uint32_t* vout = vals_alt;
-  for (int p = 0; p < passes; p++) {
-    const int shift = 8 * p;
-    k_sort_hist<<<num_tiles, SORT_THREADS, 0, stream>>>(kin, n, shift, hist, num_tiles);
-    k_sort_scan<<<256, 256, 0, stream>>>(hist, num_tiles, totals);
-    k_sort_scatter<<<num_tiles, SORT_THREADS, 0, stream>>>(kin, vin, kout, vout, n, shift, hist, totals, num_tiles);
-    std::swap(kin, kout);
-    std::swap(vin, vout);
-  }
-  RT_CUDA_TRY(cudaGetLastError(), err);
-  return RT_OK;
-}
-
-// ------------------------------------------------------------------------------------------
 // build kernels
 // ------------------------------------------------------------------------------------------
 __global__ void k_init_bounds(uint32_t* bounds) {
@@ -356,7 +204,7 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
     if (rc != RT_OK) return rc;
     if (ntri > 1) k_karras<<<grid_for(N, 256), 256, 0, stream>>>(a);
     k_refit<<<grid_for(N, 256), 256, 0, stream>>>(a);
-    static const int treelet_passes = getenv("RT_TREELET_PASSES") ? atoi(getenv("RT_TREELET_PASSES")) : 2;
+    static const int treelet_passes = getenv("RT_TREELET_PASSES") ? atoi(getenv("RT_TREELET_PASSES")) : 1;
     if (ntri > 2 && refine && treelet_passes > 0) {
       RT_CUDA_TRY(tmp.get(&a.cost, 2 * N), err);
       for (int pass = 0; pass < treelet_passes; pass++) {

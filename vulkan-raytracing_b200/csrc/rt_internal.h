@@ -34,11 +34,16 @@ struct BlasHost {
 int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refine, cudaStream_t stream, std::string& err);
 void free_blas(BlasHost& b);
 
-// LSD radix sort of (key,value) pairs, 8 bits per pass over `key_bits` bits; result in
-// keys/vals (the alt buffers are scratch).  hist must hold 256*ceil(n/4096)+256 uint32.
+// One-sweep LSD radix sort of (key,value) pairs (rt_sort.cu), 8 bits per pass over `key_bits`
+// bits, stable; the result lands in keys/vals (the alt buffers are scratch).  scratch must hold
+// sort_hist_words(n) uint32.  The u32 variant can take its element count from device memory
+// (count_dev != nullptr; n_max is then the upper bound the grid and scratch are sized for).
 int sort_pairs(uint64_t* keys, uint64_t* keys_alt, uint32_t* vals, uint32_t* vals_alt, uint64_t n, int key_bits,
-               uint32_t* hist, cudaStream_t stream, std::string& err);
+               uint32_t* scratch, cudaStream_t stream, std::string& err);
+int sort_pairs_u32(uint32_t* keys, uint32_t* keys_alt, uint32_t* vals, uint32_t* vals_alt, uint64_t n_max,
+                   const uint32_t* count_dev, int key_bits, uint32_t* scratch, cudaStream_t stream, std::string& err);
 size_t sort_hist_words(uint64_t n);
+int sort_launches(int key_bits);
 
 // Per-scene wavefront buffers and the frame pipeline.
 struct FramePipeline;

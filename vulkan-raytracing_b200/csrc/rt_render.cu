@@ -459,7 +459,7 @@ __device__ __forceinline__ uint32_t spread3_10(uint32_t v) {
   v = (v | (v << 2)) & 0x09249249u;
   return v;
 }
-__device__ __forceinline__ uint64_t ray_sort_key(const SceneDev& s, f3 o, f3 d) {
+__device__ __forceinline__ uint32_t ray_sort_key(const SceneDev& s, f3 o, f3 d, int bits) {
   const float cx = fminf(fmaxf((o.x - s.slo[0]) * s.sinv[0], 0.0f), 0.9999f);
   const float cy = fminf(fmaxf((o.y - s.slo[1]) * s.sinv[1], 0.0f), 0.9999f);
   const float cz = fminf(fmaxf((o.z - s.slo[2]) * s.sinv[2], 0.0f), 0.9999f);
@@ -469,7 +469,7 @@ __device__ __forceinline__ uint64_t ray_sort_key(const SceneDev& s, f3 o, f3 d) 
   const uint32_t qx = (uint32_t)fminf(fmaf(d.x * il, 4.0f, 4.0f), 7.0f), qy = (uint32_t)fminf(fmaf(d.y * il, 4.0f, 4.0f), 7.0f),
                  qz = (uint32_t)fminf(fmaf(d.z * il, 4.0f, 4.0f), 7.0f);
   const uint32_t dm = (spread3_10(qx) << 2) | (spread3_10(qy) << 1) | spread3_10(qz);
-  return ((uint64_t)om << 9) | (uint64_t)(dm & 0x1FFu);
+  return ((om << 9) | (dm & 0x1FFu)) >> (30 - bits);  // keep the most significant `bits`
 }
 
 // ---- mirror / refraction: next bounce ----------------------------------------------------------
@@ -477,7 +477,7 @@ __global__ void __launch_bounds__(256)
     k_shade_spec(SceneDev scene, const uint32_t* __restrict__ cnt, uint32_t* __restrict__ cntNext,
                  const uint32_t* __restrict__ qSpec, const float4* __restrict__ rayO, const float4* __restrict__ rayD,
                  const uint4* __restrict__ hits, float4* __restrict__ nextO, float4* __restrict__ nextD,
-                 uint64_t* __restrict__ skeys, uint32_t* __restrict__ svals) {
+                 uint32_t* __restrict__ skeys, uint32_t* __restrict__ svals, int sort_bits) {
   const uint32_t n = cnt[C_NSPEC];
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -502,7 +502,7 @@ __global__ void __launch_bounds__(256)
       nextO[dst] = make_float4(o.x, o.y, o.z, slot);
       nextD[dst] = make_float4(d.x, d.y, d.z, 0.0f);
       if (skeys) {
-        skeys[dst] = ray_sort_key(scene, o, d);
+        skeys[dst] = ray_sort_key(scene, o, d, sort_bits);
         svals[dst] = dst;
       }
     }
@@ -592,7 +592,7 @@ struct FramePipeline {
   uint32_t *qMiss = nullptr, *qDiff = nullptr, *qSpec = nullptr;
   float4* shadowQ = nullptr;
   float4* sample = nullptr;
-  uint64_t* sortK[2] = {nullptr, nullptr};
+  uint32_t* sortK[2] = {nullptr, nullptr};
   uint32_t* sortV[2] = {nullptr, nullptr};
   uint32_t* sortH = nullptr;
   uint32_t* cnt = nullptr;
@@ -637,7 +637,7 @@ static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std:
     RT_CUDA_TRY(cudaMalloc(&p->shadowQ, slots * 3 * sizeof(float4)), err);
     RT_CUDA_TRY(cudaMalloc(&p->sample, slots * sizeof(float4)), err);
     for (int i = 0; i < 2; i++) {
-      RT_CUDA_TRY(cudaMalloc(&p->sortK[i], slots * sizeof(uint64_t)), err);
+      RT_CUDA_TRY(cudaMalloc(&p->sortK[i], slots * sizeof(uint32_t)), err);
       RT_CUDA_TRY(cudaMalloc(&p->sortV[i], slots * sizeof(uint32_t)), err);
     }
     RT_CUDA_TRY(cudaMalloc(&p->sortH, sort_hist_words(slots) * sizeof(uint32_t)), err);
@@ -695,7 +695,8 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   static const int refill_t = getenv("RT_REFILL") ? atoi(getenv("RT_REFILL")) : 0;
   static const int tri_t = getenv("RT_TRITHRESH") ? atoi(getenv("RT_TRITHRESH")) : 8;
   static const int sort_from = getenv("RT_SORT_FROM") ? atoi(getenv("RT_SORT_FROM")) : 1000;
-  static const int sort_bits = getenv("RT_SORT_BITS") ? atoi(getenv("RT_SORT_BITS")) : 30;
+  static const int sort_to = getenv("RT_SORT_TO") ? atoi(getenv("RT_SORT_TO")) : 1000;
+  static const int sort_bits = std::min(30, std::max(8, getenv("RT_SORT_BITS") ? atoi(getenv("RT_SORT_BITS")) : 16));
   static const bool wave_on = getenv("RT_WAVE") ? atoi(getenv("RT_WAVE")) != 0 : false;
   static const int wave_refill = getenv("RT_WAVE_REFILL") ? atoi(getenv("RT_WAVE_REFILL")) : 12;
   static const int wave_tri = getenv("RT_WAVE_TRI") ? atoi(getenv("RT_WAVE_TRI")) : 6;
@@ -752,25 +753,25 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     launches += 4;
     last_bounce = j;
     if (j < U.max_bounce) {
-      const bool sorting = accel != ACCEL_BRUTE && (int)(j + 1) >= sort_from;
+      const bool sorting = accel != ACCEL_BRUTE && (int)(j + 1) >= sort_from && (int)(j + 1) <= sort_to;
       k_shade_spec<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, cn, p->qSpec, p->rayO[cur], p->rayD[cur], p->hits,
                                                    p->rayO[cur ^ 1], p->rayD[cur ^ 1], sorting ? p->sortK[0] : nullptr,
-                                                   sorting ? p->sortV[0] : nullptr);
+                                                   sorting ? p->sortV[0] : nullptr, sort_bits);
       launches++;
       cur ^= 1;
       perm = nullptr;
       // deep bounce limits (MAX_BOUNCE_COUNT 63): stop as soon as no ray survives
-      if (j >= 3 || sorting) {
+      if (sorting) {  // reorder the next bounce's rays; the count stays on the device
+        int rc2 = sort_pairs_u32(p->sortK[0], p->sortK[1], p->sortV[0], p->sortV[1], p->cap, cn + C_NRAY, sort_bits, p->sortH, st, err);
+        if (rc2 != RT_OK) return rc2;
+        launches += sort_launches(sort_bits);
+        perm = p->sortV[0];
+      }
+      if (j >= 3) {
         uint32_t alive = 0;
         RT_CUDA_TRY(cudaMemcpyAsync(&alive, cn + C_NRAY, sizeof alive, cudaMemcpyDeviceToHost, st), err);
         RT_CUDA_TRY(cudaStreamSynchronize(st), err);
         if (alive == 0) break;
-        if (sorting) {
-          int rc2 = sort_pairs(p->sortK[0], p->sortK[1], p->sortV[0], p->sortV[1], alive, sort_bits, p->sortH, st, err);
-          if (rc2 != RT_OK) return rc2;
-          launches += 3 * (((sort_bits + 7) / 8 + 1) & ~1);
-          perm = p->sortV[0];
-        }
       }
     }
   }

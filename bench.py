@@ -37,11 +37,15 @@ WORKLOADS = {
     "c3": ("c3_scene", 3840, 2160, 8, 4),
     "c4": ("c3_scene", 7680, 4320, 8, 4),
     "c2": ("c2_scene", 1920, 1080, 4, 4),
+    "c5a": ("c5a_scene", 3840, 2160, 8, 4),
+    "c5b": ("c5b_scene", 3840, 2160, 8, 4),
 }
 WORKLOAD_TEXT = {
     "c3": "C3 armadillo_standin(327680 tri, refractive, T(0,0,5)) + teapot(diffuse, shadow rays) 3840x2160 spp4 depth8",
     "c4": "C4 armadillo_standin(327680 tri, refractive) + teapot(diffuse) 7680x4320 spp4 depth8, tile-sharded",
     "c2": "C2 teapot(mirror) + teapot(refractive, T(0,0,5)) 1920x1080 spp4 depth4",
+    "c5a": "C5a 16x16 armadillo_standin grid flattened into one mesh (83.9 M tri, diffuse) 3840x2160 spp4 depth8, camera pulled back",
+    "c5b": "C5b one armadillo_standin BLAS x 256 instances (diffuse/refractive alternating) 3840x2160 spp4 depth8, camera pulled back",
 }
 CPU_CROP_FRACTION = 3  # the CPU arm renders the centred (W/3 x H/3) crop of the frame
 
@@ -55,6 +59,7 @@ def parse_args():
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--accel", type=int, default=0, help="RT_ACCEL_*: 0 = default (binary BVH), 3 = compressed 8-wide BVH")
+    ap.add_argument("--flags", type=int, default=0, help="extra rt_scene_desc flags, e.g. 16 = RT_FLAG_NO_REFINE")
     ap.add_argument("--sky", type=int, default=2048, help="procedural skybox face size")
     return ap.parse_args()
 
@@ -193,7 +198,8 @@ def main():
         import scenes
         inputs = getattr(scenes, builder)(rt, sky_size=args.sky)
         params = rt.FrameParams.make(W, H, depth, spp)
-        v, ms, cores, sample = cpu_arm(rt, inputs, rt.CameraVectors.default(), params, args.steps, args.warmup)
+        cam_ref = scenes.c5_camera(rt) if wl.startswith("c5") else rt.CameraVectors.default()
+        v, ms, cores, sample = cpu_arm(rt, inputs, cam_ref, params, args.steps, args.warmup)
         print(json.dumps({
             "impl": "reference", "metric": "Mrays/s", "value": round(v, 3), "unit": "Mrays/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
@@ -215,10 +221,10 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
     inputs = getattr(scenes, builder)(rt, sky_size=args.sky)
-    scene = rt.Scene(inputs, device_id=local_rank, accel=args.accel)
+    scene = rt.Scene(inputs, device_id=local_rank, accel=args.accel | args.flags)
     build_ms = scene.stats()["build_ms"]
     scene.set_stream(torch.cuda.current_stream().cuda_stream)
-    cam = rt.CameraVectors.default()
+    cam = scenes.c5_camera(rt) if wl.startswith("c5") else rt.CameraVectors.default()
     sharded = world > 1
     p_dev = rt.FrameParams.make(W, H, depth, spp, output_location=rt.LOCATION_DEVICE,
                                 shard_index=rank if sharded else 0, shard_count=world if sharded else 1)

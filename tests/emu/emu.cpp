@@ -14,6 +14,7 @@
 #include "rt_b200.h"
 #include "rt_build.cuh"
 #include "rt_shade.cuh"
+#include "rt_tlas.hpp"
 
 using namespace rt;
 
@@ -38,8 +39,11 @@ struct EmuScene {
   std::vector<uint8_t> sky;
   uint32_t sky_w = 0, sky_h = 0;
   uint32_t accel = 0;
+  std::vector<float4> tlas;
   SceneDev dev() const {
     SceneDev s{};
+    s.tlas = tlas.empty() ? nullptr : tlas.data();
+    s.n_tlas = (uint32_t)(tlas.size() / 4);
     s.blas = blas_dev.data(); s.inst = inst.data(); s.n_inst = (uint32_t)inst.size(); s.accel = accel;
     s.sky = sky.empty() ? nullptr : sky.data(); s.sky_w = sky_w; s.sky_h = sky_h;
     return s;
@@ -191,6 +195,7 @@ int emu_scene_create(const rt_scene_desc* d, void** out) {
     s->inst[i].mesh = d->instances[i].mesh; s->inst[i].type = d->instances[i].type;
     set_instance(*s, i, d->instances[i].transform);
   }
+  build_tlas(s->inst, s->tlas);
   if (d->skybox_rgba8 && d->sky_w) {
     s->sky_w = d->sky_w; s->sky_h = d->sky_h;
     s->sky.assign(d->skybox_rgba8, d->skybox_rgba8 + (size_t)6 * d->sky_w * d->sky_h * 4);

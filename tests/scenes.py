@@ -74,3 +74,61 @@ def hash_cases(rt):
          rt.FrameParams.make(240, 135, 4, 4)),
         ("smoke_160x120_d6", smoke_scene(rt), rt.FrameParams.make(160, 120, 6, 4)),
     ]
+
+
+def instanced_grid_scene(rt, nx=4, nz=3, level=2, sky_size=16):
+    """Small stand-in for config C5b: one mesh, nx*nz instances on the XZ plane with alternating
+    diffuse / refractive types plus a mirror teapot: enough instances for the top-level tree."""
+    import math
+    av, ai = rt.make_standin_armadillo(level)
+    tv, ti = teapot()
+    inst = []
+    for iz in range(nz):
+        for ix in range(nx):
+            t = rt.translation34(6.0 * (ix - (nx - 1) / 2), -1.0 + 0.5 * ((ix + iz) % 3), -6.0 * iz)
+            if (ix + iz) % 4 == 1:   # a few rotated instances
+                a = 0.3 * (ix + 1)
+                t = np.array([math.cos(a), 0, math.sin(a), t[3], 0, 1, 0, t[7], -math.sin(a), 0, math.cos(a), t[11]], np.float32)
+            inst.append((0, rt.TYPE_DIFFUSE if (ix + iz) & 1 else rt.TYPE_REFRACTIVE, t))
+    inst.append((1, rt.TYPE_MIRROR, rt.translation34(0, -4, 4)))
+    return rt.SceneInputs([(av, ai), (tv, ti)], inst, rt.make_procedural_skybox(sky_size))
+
+
+GRID_PITCH = 6.0   # 1.2 x the stand-in's width (radius 2.5)
+
+
+def look_at_camera(rt, position, target):
+    """Camera vectors for a camera at `position` looking at `target`, built the way the reference's
+    Camera class derives them (camera.cpp:16-25): right = normalize(-f.z, 0, f.x), up = right x front."""
+    p, t = np.asarray(position, np.float64), np.asarray(target, np.float64)
+    f = (t - p) / np.linalg.norm(t - p)
+    r = np.array([-f[2], 0.0, f[0]])
+    r /= np.linalg.norm(r)
+    u = np.cross(r, f)
+    return rt.CameraVectors.make(p, r, u, f)
+
+
+def c5_camera(rt, n=16):
+    """Pulled back so the n x n grid fills the 2.5-focal-length view (half angle atan(1/2.5))."""
+    half = 0.5 * n * GRID_PITCH
+    return look_at_camera(rt, (0.0, 1.25 * half, 2.9 * half), (0.0, 0.0, 0.0))
+
+
+def c5a_scene(rt, n=16, level=7, sky_size=2048):
+    """BASELINE config C5a: n x n stand-in armadillos flattened into ONE mesh (16x16 at level 7 =
+    83.9 M triangles), diffuse: stresses the LBVH build and node fetches from HBM."""
+    av, ai = rt.make_standin_armadillo(level)
+    gv, gi = rt.make_grid(av, ai, n, n, GRID_PITCH)
+    return rt.SceneInputs([(gv, gi)], [(0, rt.TYPE_DIFFUSE, rt.IDENTITY34)], rt.make_procedural_skybox(sky_size))
+
+
+def c5b_scene(rt, n=16, level=7, sky_size=2048):
+    """BASELINE config C5b: one stand-in BLAS + n*n instance transforms, types alternating diffuse /
+    refractive by (ix+iz)&1: exercises the top-level tree."""
+    av, ai = rt.make_standin_armadillo(level)
+    inst = []
+    for iz in range(n):
+        for ix in range(n):
+            inst.append((0, rt.TYPE_REFRACTIVE if (ix + iz) & 1 else rt.TYPE_DIFFUSE,
+                         rt.translation34((ix - 0.5 * (n - 1)) * GRID_PITCH, 0.0, (iz - 0.5 * (n - 1)) * GRID_PITCH)))
+    return rt.SceneInputs([(av, ai)], inst, rt.make_procedural_skybox(sky_size))

@@ -40,6 +40,11 @@ def test_rotated_instances_and_camera(rt, ob, emu):
     compare(rt, ob, emu, inputs, rt.FrameParams.make(90, 60, 5, 2), 0, cam.vectors())
 
 
+@pytest.mark.parametrize("accel", [0, 3])
+def test_many_instances_use_the_top_level_tree(rt, ob, emu, accel):
+    compare(rt, ob, emu, scenes.instanced_grid_scene(rt), rt.FrameParams.make(120, 80, 5, 2), accel)
+
+
 def test_tiny_and_degenerate_meshes(rt, ob, emu):
     cv, ci = scenes.unit_cube()
     one = (np.array([[-3, -3, 0, 0, 0, 1], [3, -3, 0, 0, 0, 1], [0, 3, 0, 0, 0, 1]], np.float32),

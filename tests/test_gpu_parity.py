@@ -3,6 +3,8 @@
 numeric contract, so RGBA32F is expected bit-identical and RGBA8 identical; the stated
 tolerance from BASELINE.json (<= 2/255 per channel, PSNR >= 45 dB, >= 99.99 % primary ids) is
 asserted as the floor."""
+import os
+
 import numpy as np
 import pytest
 
@@ -99,6 +101,46 @@ def test_set_transforms_matches_rebuild(gpu_rt, ob):
     osc.set_transforms(xf)
     assert np.array_equal(img, osc.render(cam, p)["rgba8"])
     sc.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("accel", [0, 3])
+def test_instanced_grid_top_level_tree(gpu_rt, ob, accel):
+    """13 instances (> RT_TLAS_MIN_INSTANCES): rays walk the top-level tree; also after a transform update."""
+    rt = gpu_rt
+    inputs = scenes.instanced_grid_scene(rt)
+    check_frame(rt, ob, inputs, rt.FrameParams.make(240, 160, 5, 4), accel)
+
+
+def test_headless_host_frames_match_the_python_binding(gpu_rt, tmp_path):
+    """rt_headless renders the orbit animation through the C ABI from C++; its PPM frames are
+    bit-identical to the same frames rendered through the ctypes binding."""
+    import subprocess
+    rt = gpu_rt
+    exe = os.path.join(rt.REPO_ROOT, "vulkan-raytracing_b200", "rt_headless")
+    prefix = str(tmp_path / "f")
+    r = subprocess.run([exe, "--center", "standin:3", "--orbiting", "standin:4", "--center-type", "1", "--orbiting-type", "2",
+                        "--skybox", "procedural:64", "--size", "160x120", "--bounces", "5", "--spp", "2", "--frames", "3",
+                        "--dt", "0.5", "--out", prefix, "--fps"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "FPS:" in r.stdout
+    a, ai = rt.make_standin_armadillo(3)
+    b, bi = rt.make_standin_armadillo(4)
+    inputs = rt.SceneInputs([(a, ai), (b, bi)], [(0, rt.TYPE_MIRROR, rt.IDENTITY34), (1, rt.TYPE_REFRACTIVE, rt.IDENTITY34)],
+                            rt.make_procedural_skybox(64))
+    scene = rt.Scene(inputs, device_id=0)
+    p = rt.FrameParams.make(160, 120, 5, 2)
+    cam = rt.Camera().vectors()
+    for f in range(3):
+        scene.set_transforms(rt.orbit_transforms(np.float32(f) * np.float32(0.5) * np.float32(0.1)))
+        img = scene.render(cam, p)
+        with open(f"{prefix}_{f:04d}.ppm", "rb") as fh:
+            assert fh.readline().strip() == b"P6"
+            w, h = map(int, fh.readline().split())
+            assert fh.readline().strip() == b"255"
+            ppm = np.frombuffer(fh.read(), np.uint8).reshape(h, w, 3)
+        assert np.array_equal(ppm, img[:, :, :3]), f"frame {f} differs"
+    scene.close()
 
 
 def test_trace_rays_closest_and_any(gpu_rt, ob):

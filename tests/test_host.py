@@ -147,3 +147,21 @@ def test_frame_shard_sizes(rt):
     assert lib.rt_frame_output_bytes(C.byref(p)) == ((tiles + 2) // 3) * 512 * 4
     q = rt.FrameParams.make(200, 136, 1, 1, output_format=rt.FORMAT_RGBA32F)
     assert lib.rt_frame_output_bytes(C.byref(q)) == 200 * 136 * 16
+
+
+HEADLESS = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "vulkan-raytracing_b200", "rt_headless")
+
+
+def test_headless_host_usage_and_no_device(rt):
+    """rt_headless (the C++ replacement of the reference's main()) is built, documents the config.h
+    options, and refuses to run without a CUDA device instead of falling back."""
+    import subprocess
+    r = subprocess.run([HEADLESS, "--help"], capture_output=True, text=True)
+    assert r.returncode == 0
+    for opt in ("--center", "--orbiting", "--center-type", "--skybox", "--bounces", "--spp", "--fps"):
+        assert opt in r.stdout
+    assert subprocess.run([HEADLESS, "--bogus"], capture_output=True).returncode == 1
+    if rt.device_count() == 0:
+        r = subprocess.run([HEADLESS, "--center", "standin:2", "--orbiting", "standin:2", "--skybox", "procedural:8"],
+                           capture_output=True, text=True)
+        assert r.returncode == 2 and "no CPU fallback" in r.stderr

@@ -2,6 +2,7 @@
 
   vulkan-raytracing_b200/librt_b200.so   CUDA kernels + C ABI (include/rt_b200.h), sm_100a only
   vulkan-raytracing_b200/librt_host.so   asset loading / camera (include/rt_host.h)
+  vulkan-raytracing_b200/rt_headless     headless C++ host replacing the reference's main()
   oracle/liboracle.so                    CPU checker (test infrastructure)
   oracle/_ref/*                          pieces of the real reference, only where its checkout exists
   tests/emu/libemu.so                    serial CPU build of the device functions (tests only)
@@ -69,6 +70,19 @@ def build_host(force=False):
     return out
 
 
+def build_headless(force=False):
+    """rt_headless: the C++ host that replaces the reference's main() (links both C ABIs)."""
+    src = os.path.join(HERE, "host", "rt_headless.cpp")
+    out = os.path.join(HERE, "rt_headless")
+    deps = [src, os.path.join(HERE, "host", "config.hpp"), os.path.join(ROOT, "include", "rt_b200.h"),
+            os.path.join(ROOT, "include", "rt_host.h")]
+    if not force and not _newer(out, deps):
+        return out
+    run(["g++", "-O2", "-std=c++17", "-Wall", "-o", out, src, "-L", HERE, "-l:librt_b200.so", "-l:librt_host.so",
+         "-Wl,-rpath,$ORIGIN", "-Wl,-rpath-link," + HERE])
+    return out
+
+
 def build_oracle(force=False):
     d = os.path.join(ROOT, "oracle")
     out = os.path.join(d, "liboracle.so")
@@ -98,6 +112,7 @@ def build_all(force=False, verbose=False):
     build_oracle(force)
     build_emu(force)
     build_cuda(force, verbose)
+    build_headless(force)
 
 
 if __name__ == "__main__":

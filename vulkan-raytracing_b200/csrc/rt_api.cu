@@ -7,6 +7,7 @@
 #include <memory>
 
 #include "rt_internal.h"
+#include "rt_tlas.hpp"
 
 namespace rt {
 
@@ -20,6 +21,9 @@ struct Scene {
   std::vector<InstDev> inst;
   BlasDev* d_blas = nullptr;
   InstDev* d_inst = nullptr;
+  std::vector<float4> tlas;      // host copy of the top-level tree (rt_tlas.hpp)
+  float4* d_tlas = nullptr;
+  size_t d_tlas_cap = 0;
   uint8_t* d_sky = nullptr;
   uint32_t sky_w = 0, sky_h = 0;
   FramePipeline* pipe = nullptr;
@@ -41,8 +45,11 @@ struct Scene {
       float lo = 3.0e38f, hi = -3.0e38f;
       for (const InstDev& in : inst) { lo = std::min(lo, in.wlo[k]); hi = std::max(hi, in.whi[k]); }
       s.slo[k] = inst.empty() ? 0.0f : lo;
+      s.shi[k] = inst.empty() ? 0.0f : hi;
       s.sinv[k] = (!inst.empty() && hi > lo) ? 1.0f / (hi - lo) : 0.0f;
     }
+    s.tlas = tlas.empty() ? nullptr : d_tlas;
+    s.n_tlas = (uint32_t)(tlas.size() / 4);
     return s;
   }
 };
@@ -94,6 +101,17 @@ static void set_instance(Scene& s, uint32_t i, const float* xf) {
 
 static int upload_instances(Scene& s) {
   if (s.inst.empty()) return RT_OK;
+  build_tlas(s.inst, s.tlas);
+  if (!s.tlas.empty()) {
+    if (s.tlas.size() > s.d_tlas_cap) {
+      cudaFree(s.d_tlas);
+      s.d_tlas = nullptr;
+      s.d_tlas_cap = 0;
+      RT_CUDA_TRY(cudaMalloc(&s.d_tlas, s.tlas.size() * sizeof(float4)), g_err);
+      s.d_tlas_cap = s.tlas.size();
+    }
+    RT_CUDA_TRY(cudaMemcpyAsync(s.d_tlas, s.tlas.data(), s.tlas.size() * sizeof(float4), cudaMemcpyHostToDevice, s.stream), g_err);
+  }
   RT_CUDA_TRY(cudaMemcpyAsync(s.d_inst, s.inst.data(), s.inst.size() * sizeof(InstDev), cudaMemcpyHostToDevice, s.stream), g_err);
   RT_CUDA_TRY(cudaStreamSynchronize(s.stream), g_err);
   return RT_OK;
@@ -103,7 +121,7 @@ static void destroy_scene(Scene* s) {
   if (!s) return;
   cudaSetDevice(s->device);
   for (auto& b : s->blas) free_blas(b);
-  cudaFree(s->d_blas); cudaFree(s->d_inst); cudaFree(s->d_sky); cudaFree(s->d_out);
+  cudaFree(s->d_blas); cudaFree(s->d_inst); cudaFree(s->d_tlas); cudaFree(s->d_sky); cudaFree(s->d_out);
   pipeline_destroy(s->pipe);
   delete s;
 }

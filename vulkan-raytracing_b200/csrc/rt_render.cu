@@ -96,9 +96,13 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev scene, FrameUniforms U,
         RayObj rw;
         rw.o = o;
         rw.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
-        for (uint32_t i = 0; i < scene.n_inst && !reach; i++) {
-          const InstDev& in = scene.inst[i];
-          reach = slab_test(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], 0.001f, 10000.0f);
+        if (scene.tlas) {  // many instances: the box around all of them decides here
+          reach = slab_test(rw, scene.slo[0], scene.slo[1], scene.slo[2], scene.shi[0], scene.shi[1], scene.shi[2], 0.001f, 10000.0f);
+        } else {
+          for (uint32_t i = 0; i < scene.n_inst && !reach; i++) {
+            const InstDev& in = scene.inst[i];
+            reach = slab_test(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], 0.001f, 10000.0f);
+          }
         }
         if (reach) {
           // every sample starts as tmpColor = Iamb*ka (shader.rgen:81)
@@ -722,7 +726,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
                                                     p->qDiff, p->qSpec, prim, p->stats64, refill_t, tri_t, perm);   \
   }
     RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 0], st), err);
-    const bool wave = accel == ACCEL_WIDE && wave_on && rq.scene.n_inst <= 32u;
+    const bool wave = accel == ACCEL_WIDE && wave_on && rq.scene.tlas == nullptr;
     if (wave) {
       static int wb[2] = {0, 0};
       if (!wb[0]) { wb[0] = persistent_blocks(k_trace_wave<false>, TRACE_THREADS); wb[1] = persistent_blocks(k_trace_wave<true>, TRACE_THREADS); }

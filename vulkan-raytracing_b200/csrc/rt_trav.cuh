@@ -43,6 +43,9 @@ struct SceneDev {
   const uint8_t* sky;  // 6 x h x w x RGBA8
   uint32_t sky_w, sky_h;
   float slo[3], sinv[3];  // world bounds of all instances (origin cell of the ray sort key)
+  float shi[3];
+  const float4* tlas;     // binary tree over the instance boxes (rt_tlas.hpp); null for small scenes
+  uint32_t n_tlas;
 };
 
 struct HitRec {
@@ -348,6 +351,19 @@ RT_HD bool trace_wide(const BlasDev& b, const RayObj& r, float tmin, uint32_t in
 // The ray is taken into each instance's object space (direction not renormalised, so t
 // is shared), as the Vulkan TLAS->BLAS traversal does.  Returns true when something was
 // hit; `best` then holds the closest hit (for ANY only best.inst is meaningful).
+// one instance: cull against its padded world box, take the ray into object space, traverse
+template <class Stack, bool ANY, bool COUNT>
+RT_HD bool trace_instance(const SceneDev& s, uint32_t i, f3 o, f3 d, const RayObj& rw, bool cull, float tmin, HitRec& best,
+                          Stack& st, TravCounters* cnt) {
+  const InstDev& in = s.inst[i];
+  if (cull && !slab_test(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], tmin, best.t)) return false;
+  const RayObj r = ray_setup(xform_point(in.w2o, o), xform_vector(in.w2o, d));
+  const BlasDev b = s.blas[in.mesh];  // by value: the node / triangle base pointers stay in registers
+  if (s.accel == ACCEL_WIDE) return trace_wide<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
+  if (s.accel == ACCEL_BVH2) return trace_bvh2<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
+  return trace_brute<ANY, COUNT>(b, r, tmin, i, best, cnt);
+}
+
 template <class Stack, bool ANY, bool COUNT>
 RT_HD bool trace_scene(const SceneDev& s, f3 o, f3 d, float tmin, float tmax, HitRec& best, Stack& st,
                        TravCounters* cnt) {
@@ -356,21 +372,47 @@ RT_HD bool trace_scene(const SceneDev& s, f3 o, f3 d, float tmin, float tmax, Hi
   best.t = u2f(f2u(tmax) - 1u);  // nextafter(tmax, -inf): "t <= best.t" == "t < tmax"
   best.u = 0.0f;
   best.v = 0.0f;
-  for (uint32_t i = 0; i < s.n_inst; i++) {
-    const InstDev& in = s.inst[i];
-    if (s.n_inst > 1) {  // cull against the instance's padded world box
-      RayObj rw;
-      rw.o = o;
-      rw.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
-      if (!slab_test(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], tmin, best.t)) continue;
+  RayObj rw;  // world ray: only o and idir are used (box tests)
+  rw.o = o;
+  rw.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
+  if (s.tlas == nullptr) {  // few instances: visit them in index order
+    for (uint32_t i = 0; i < s.n_inst; i++) {
+      const bool hit = trace_instance<Stack, ANY, COUNT>(s, i, o, d, rw, s.n_inst > 1, tmin, best, st, cnt);
+      if (ANY && hit) return true;
     }
-    const RayObj r = ray_setup(xform_point(in.w2o, o), xform_vector(in.w2o, d));
-    const BlasDev b = s.blas[in.mesh];  // by value: the node / triangle base pointers stay in registers
-    bool hit;
-    if (s.accel == ACCEL_WIDE) hit = trace_wide<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
-    else if (s.accel == ACCEL_BVH2) hit = trace_bvh2<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
-    else hit = trace_brute<ANY, COUNT>(b, r, tmin, i, best, cnt);
-    if (ANY && hit) return true;
+    return best.inst != RT_MISS;
+  }
+  // top-level tree, nearest child first; the instance traversal below uses `st`, so the few
+  // pending top-level nodes live in their own small stack
+  int tstack[32];
+  int tsp = 0, node = 0;
+  while (true) {
+    if (node < 0) {
+      const bool hit = trace_instance<Stack, ANY, COUNT>(s, (uint32_t)~node, o, d, rw, false, tmin, best, st, cnt);
+      if (ANY && hit) return true;
+      if (tsp == 0) break;
+      node = tstack[--tsp];
+      continue;
+    }
+    const float8 lo8 = ldg256(&s.tlas[4 * (size_t)node]), hi8 = ldg256(&s.tlas[4 * (size_t)node + 2]);
+    const float4 n0 = lo8.a, n1 = lo8.b, n2 = hi8.a, n3 = hi8.b;
+    float tn0, tf0, tn1, tf1;
+    slab_interval(rw, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
+    slab_interval(rw, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
+    const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+    int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
+    if (h0 && h1) {
+      if (tn1 < tn0) { const int t = c0; c0 = c1; c1 = t; }
+      if (tsp < 32) tstack[tsp++] = c1;
+      node = c0;
+    } else if (h0) {
+      node = c0;
+    } else if (h1) {
+      node = c1;
+    } else {
+      if (tsp == 0) break;
+      node = tstack[--tsp];
+    }
   }
   return best.inst != RT_MISS;
 }

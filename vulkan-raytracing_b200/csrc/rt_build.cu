@@ -109,10 +109,15 @@ __global__ void __launch_bounds__(256) k_refit(BuildArrays a) {
     refit_from_leaf(a, j);
 }
 
-// one SAH treelet-refinement pass (rt_build.cuh): thread j climbs from sorted leaf j
-__global__ void __launch_bounds__(128) k_treelet(BuildArrays a) {
+// SAH treelet refinement (rt_build.cuh), one launch per bottom-up round
+__global__ void __launch_bounds__(256) k_treelet_leaves(BuildArrays a, uint32_t* queue, uint32_t* qcount) {
   for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < a.ntri; j += gridDim.x * blockDim.x)
-    treelet_from_leaf(a, j);
+    treelet_leaf_arrive(a, j, queue, qcount);
+}
+__global__ void __launch_bounds__(128) k_treelet_round(BuildArrays a, const uint32_t* __restrict__ queue, uint32_t count,
+                                                       uint32_t* next_queue, uint32_t* next_count) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
+    treelet_round_node(a, queue[i], next_queue, next_count);
 }
 
 __global__ void __launch_bounds__(128) k_collapse(BuildArrays a, uint32_t begin, uint32_t end) {
@@ -207,9 +212,25 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
     static const int treelet_passes = getenv("RT_TREELET_PASSES") ? atoi(getenv("RT_TREELET_PASSES")) : 1;
     if (ntri > 2 && refine && treelet_passes > 0) {
       RT_CUDA_TRY(tmp.get(&a.cost, 2 * N), err);
+      uint32_t* queue[2] = {nullptr, nullptr};
+      uint32_t* qcount = nullptr;  // [2]
+      RT_CUDA_TRY(tmp.get(&queue[0], N), err);
+      RT_CUDA_TRY(tmp.get(&queue[1], N), err);
+      RT_CUDA_TRY(tmp.get(&qcount, 2), err);
       for (int pass = 0; pass < treelet_passes; pass++) {
         RT_CUDA_TRY(cudaMemsetAsync(a.flags, 0, N * sizeof(uint32_t), stream), err);
-        k_treelet<<<grid_for(N, 128), 128, 0, stream>>>(a);
+        RT_CUDA_TRY(cudaMemsetAsync(qcount, 0, 2 * sizeof(uint32_t), stream), err);
+        k_treelet_leaves<<<grid_for(N, 256), 256, 0, stream>>>(a, queue[0], qcount);
+        int cur = 0;
+        for (int round = 0; round < 4096; round++) {
+          uint32_t count = 0;
+          RT_CUDA_TRY(cudaMemcpyAsync(&count, qcount + cur, sizeof count, cudaMemcpyDeviceToHost, stream), err);
+          RT_CUDA_TRY(cudaStreamSynchronize(stream), err);
+          if (count == 0) break;
+          RT_CUDA_TRY(cudaMemsetAsync(qcount + (cur ^ 1), 0, sizeof(uint32_t), stream), err);
+          k_treelet_round<<<grid_for(count, 128), 128, 0, stream>>>(a, queue[cur], count, queue[cur ^ 1], qcount + (cur ^ 1));
+          cur ^= 1;
+        }
       }
     }
   }

@@ -216,15 +216,35 @@ RT_HD void treelet_optimize_node(const BuildArrays& a, int x) {
   const int S = 1 << nl;
   float area[1 << TREELET_LEAVES], copt[1 << TREELET_LEAVES];
   uint8_t part[1 << TREELET_LEAVES];
-  for (int s = 1; s < S; s++) {
-    float lx = 3.0e38f, ly = 3.0e38f, lz = 3.0e38f, hx = -3.0e38f, hy = -3.0e38f, hz = -3.0e38f;
-    for (int i = 0; i < nl; i++)
-      if (s & (1 << i)) {
-        lx = fminf(lx, llo[i].x); ly = fminf(ly, llo[i].y); lz = fminf(lz, llo[i].z);
-        hx = fmaxf(hx, lhi[i].x); hy = fmaxf(hy, lhi[i].y); hz = fmaxf(hz, lhi[i].z);
-      }
-    const float dx = hx - lx, dy = hy - ly, dz = hz - lz;
-    area[s] = dx * dy + dy * dz + dz * dx;
+  {
+    // area of the union box of every leaf subset: boxes of the 16 subsets of leaves 0-3 and of
+    // the 8 subsets of leaves 4-6 first, then one union per subset
+    float lob[16][6], hib[8][6];
+    for (int m = 0; m < 16; m++) {
+      float lx = 3.0e38f, ly = 3.0e38f, lz = 3.0e38f, hx = -3.0e38f, hy = -3.0e38f, hz = -3.0e38f;
+      for (int i = 0; i < 4 && i < nl; i++)
+        if (m & (1 << i)) {
+          lx = fminf(lx, llo[i].x); ly = fminf(ly, llo[i].y); lz = fminf(lz, llo[i].z);
+          hx = fmaxf(hx, lhi[i].x); hy = fmaxf(hy, lhi[i].y); hz = fmaxf(hz, lhi[i].z);
+        }
+      lob[m][0] = lx; lob[m][1] = ly; lob[m][2] = lz; lob[m][3] = hx; lob[m][4] = hy; lob[m][5] = hz;
+    }
+    for (int m = 0; m < 8; m++) {
+      float lx = 3.0e38f, ly = 3.0e38f, lz = 3.0e38f, hx = -3.0e38f, hy = -3.0e38f, hz = -3.0e38f;
+      for (int i = 4; i < nl; i++)
+        if (m & (1 << (i - 4))) {
+          lx = fminf(lx, llo[i].x); ly = fminf(ly, llo[i].y); lz = fminf(lz, llo[i].z);
+          hx = fmaxf(hx, lhi[i].x); hy = fmaxf(hy, lhi[i].y); hz = fmaxf(hz, lhi[i].z);
+        }
+      hib[m][0] = lx; hib[m][1] = ly; hib[m][2] = lz; hib[m][3] = hx; hib[m][4] = hy; hib[m][5] = hz;
+    }
+    for (int s = 1; s < S; s++) {
+      const float* a0 = lob[s & 15];
+      const float* a1 = hib[s >> 4];
+      const float dx = fmaxf(a0[3], a1[3]) - fminf(a0[0], a1[0]), dy = fmaxf(a0[4], a1[4]) - fminf(a0[1], a1[1]),
+                  dz = fmaxf(a0[5], a1[5]) - fminf(a0[2], a1[2]);
+      area[s] = dx * dy + dy * dz + dz * dx;
+    }
   }
   for (int i = 0; i < nl; i++) copt[1 << i] = lcost[i];
   for (int sz = 2; sz <= nl; sz++)
@@ -278,7 +298,26 @@ RT_HD void treelet_optimize_node(const BuildArrays& a, int x) {
   }
 }
 
-// bottom-up driver of one refinement pass, started once per leaf j (sorted position)
+// Round-based driver (GPU): a node is ready when both children are final.  Round 0 = the
+// parents that two leaves reached; every round refines all ready nodes (one thread each, all
+// lanes busy) and queues the parents that became ready.  The tree height bounds the rounds.
+RT_HD void treelet_leaf_arrive(const BuildArrays& a, uint32_t j, uint32_t* queue, uint32_t* qcount) {
+  const int n = (int)a.ntri;
+  const int leaf = (n - 1) + (int)j;
+  a.cost[leaf] = RT_SAH_CI * half_area(a.node_lo[leaf], a.node_hi[leaf]);
+  if (n == 1) return;
+  const int p = a.parent[leaf];
+  if (RT_ATOMIC_ADD(&a.flags[p], 1u) == 1u) queue[RT_ATOMIC_ADD(qcount, 1u)] = (uint32_t)p;
+}
+RT_HD void treelet_round_node(const BuildArrays& a, uint32_t node, uint32_t* next_queue, uint32_t* next_count) {
+  treelet_optimize_node(a, (int)node);
+  if (node == 0u) return;
+  const int p = a.parent[node];
+  if (RT_ATOMIC_ADD(&a.flags[p], 1u) == 1u) next_queue[RT_ATOMIC_ADD(next_count, 1u)] = (uint32_t)p;
+}
+
+// bottom-up driver of one refinement pass, started once per leaf j (sorted position): the serial
+// (emulation) schedule; it refines the same treelets in another valid bottom-up order
 RT_HD void treelet_from_leaf(const BuildArrays& a, uint32_t j) {
   const int n = (int)a.ntri;
   const int leaf = (n - 1) + (int)j;

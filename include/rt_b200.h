@@ -210,7 +210,8 @@ int rt_primary_hits(void* scene, const rt_camera* camera, const rt_frame_params*
                     rt_hit* hits_out);
 /* Closest-hit (any_hit = 0) or any-hit (any_hit = 1) traces of an arbitrary ray
  * batch: traceRayEXT of shader.rgen:86 / :111.  origins/dirs: n x 3 floats
- * (HOST); tmin/tmax scalars.  For any_hit only hits_out[i].instance (0 or
+ * (HOST); tmin/tmax scalars with 0 <= tmin <= tmax, as Vulkan requires of traceRayEXT
+ * (RT_ERR_INVALID_ARGUMENT otherwise).  For any_hit only hits_out[i].instance (0 or
  * 0xFFFFFFFF) is meaningful. */
 int rt_trace_rays(void* scene, uint64_t n, const float* origins, const float* dirs,
                   float tmin, float tmax, int any_hit, rt_hit* hits_out);

@@ -373,6 +373,9 @@ int rt_trace_rays(void* scene, uint64_t n, const float* origins, const float* di
                   rt_hit* hits_out) {
   Scene* s = (Scene*)scene;
   if (!s || (n && (!origins || !dirs || !hits_out))) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  // traceRayEXT requires 0 <= tmin <= tmax (Vulkan VUID-RuntimeSpirv-OpTraceRayKHR-06552..06553);
+  // the conservative box tests rely on it
+  if (!(tmin >= 0.0f) || !(tmax >= tmin)) return fail(RT_ERR_INVALID_ARGUMENT, "need 0 <= tmin <= tmax");
   if (n == 0) return RT_OK;
   RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
   float *d_o = nullptr, *d_d = nullptr;

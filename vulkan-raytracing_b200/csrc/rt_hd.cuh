@@ -33,8 +33,12 @@ static inline uint2 make_uint2(uint32_t x, uint32_t y) { return uint2{x, y}; }
 
 #if defined(__CUDA_ARCH__)
 #define RT_LDG(p) __ldg(p)
+// true when any lane of the warp that is currently executing with this one has p set; a
+// scheduling hint only (results never depend on it), the serial emulation sees one lane
+#define RT_ANY_LANE(p) __any_sync(__activemask(), (p))
 #else
 #define RT_LDG(p) (*(p))
+#define RT_ANY_LANE(p) (p)
 #endif
 
 namespace rt {

@@ -50,6 +50,10 @@ struct HybridStack {
     --sp;
     return sp < STACK_SM ? sm[sp * TRACE_THREADS] : loc[sp - STACK_SM];
   }
+  // 32-bit entries (binary traversal); a packed 2 x STACK_SM word view of the same storage
+  // measured 4 % slower than simply using the low half of an 8-byte slot
+  __device__ __forceinline__ void push1(uint32_t v) { push(make_uint2(v, 0u)); }
+  __device__ __forceinline__ uint32_t pop1() { return pop().x; }
 };
 
 template <int ACCEL, bool ANY, bool COUNT>

@@ -183,31 +183,91 @@ RT_HD void slab_interval(const RayObj& r, float lox, float loy, float loz, float
   tf = fminf(fmaf(1e-5f, fabsf(f), f), tmax);
 }
 
+// Ordered traversal with a postponed leaf (Aila & Laine 2009, "speculative traversal").  Leaves
+// are single triangles and turn up once per ~15 node visits, at different moments in different
+// lanes: tested on the spot, the triangle code ran with 5 of 32 lanes and took 38 % of the issue
+// slots (ncu, bounce 1 of C3).  Instead a lane parks the first leaf it reaches and keeps
+// walking; the warp leaves the node loop when every lane holds a leaf (or a second one, or has
+// run out of nodes), and the triangle tests then run together.  The price is a few node visits
+// made with a stale best.t.
+static const int RT_NO_LEAF = 0x7FFFFFFF;
+
 template <class Stack, bool ANY, bool COUNT>
-RT_HD bool trace_bvh2(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
-                      TravCounters* cnt) {
-  if (b.ntri == 0) return false;
-  if (b.ntri == 1) return test_leaf_tri<ANY, COUNT>(b, 0, r, tmin, inst, best, cnt);
+RT_HD bool trace_bvh2_parked(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
+                             TravCounters* cnt) {
+  st.reset();
+  int node = 0, parked = RT_NO_LEAF;
+  bool walking = true;  // `node` is valid (an inner node to visit or a leaf to test)
+  while (true) {
+    while (walking && node >= 0) {
+      const float8 lo8 = ldg256(&b.nodes[4 * (size_t)node]), hi8 = ldg256(&b.nodes[4 * (size_t)node + 2]);
+      const float4 n0 = lo8.a, n1 = lo8.b, n2 = hi8.a, n3 = hi8.b;
+      if (COUNT) cnt->nodes++;
+      float tn0, tf0, tn1, tf1;
+      slab_interval(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
+      slab_interval(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
+      const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+      int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
+      if (h0 && h1) {
+        if (tn1 < tn0) { const int t = c0; c0 = c1; c1 = t; }
+        st.push1((uint32_t)c1);
+        node = c0;
+      } else if (h0) {
+        node = c0;
+      } else if (h1) {
+        node = c1;
+      } else if (!st.empty()) {
+        node = (int)st.pop1();
+      } else {
+        walking = false;
+      }
+      if (walking && node < 0 && parked == RT_NO_LEAF) {  // park the first leaf and walk on
+        parked = node;
+        if (!st.empty()) node = (int)st.pop1();
+        else walking = false;
+      }
+      if (!RT_ANY_LANE(parked == RT_NO_LEAF && walking)) break;  // every lane has something to test
+    }
+    if (parked != RT_NO_LEAF) {
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~parked, r, tmin, inst, best, cnt)) return true;
+      parked = RT_NO_LEAF;
+    }
+    if (walking && node < 0) {
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
+      if (!st.empty()) node = (int)st.pop1();
+      else walking = false;
+    }
+    if (!walking) break;
+  }
+  return false;
+}
+
+// Ordered traversal, leaves tested as they are reached (best.t shrinks as early as possible).
+template <class Stack, bool ANY, bool COUNT>
+RT_HD bool trace_bvh2_direct(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
+                             TravCounters* cnt) {
   st.reset();
   int node = 0;
   while (true) {
     if (node < 0) {
       if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
       if (st.empty()) break;
-      node = (int)st.pop().x;
+      node = (int)st.pop1();
       continue;
     }
     const float8 lo8 = ldg256(&b.nodes[4 * (size_t)node]), hi8 = ldg256(&b.nodes[4 * (size_t)node + 2]);
     const float4 n0 = lo8.a, n1 = lo8.b, n2 = hi8.a, n3 = hi8.b;
     if (COUNT) cnt->nodes++;
     float tn0, tf0, tn1, tf1;
+    // (a one-fma-per-plane form with the margins folded into per-ray constants was measured: 12 more
+    // live registers cost more than the 16 instructions per node it saves, profiles/r01_sweep_boxtest.txt)
     slab_interval(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
     slab_interval(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
     const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
     int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
     if (h0 && h1) {
       if (tn1 < tn0) { const int t = c0; c0 = c1; c1 = t; }
-      st.push(make_uint2((uint32_t)c1, 0u));
+      st.push1((uint32_t)c1);
       node = c0;
     } else if (h0) {
       node = c0;
@@ -215,10 +275,22 @@ RT_HD bool trace_bvh2(const BlasDev& b, const RayObj& r, float tmin, uint32_t in
       node = c1;
     } else {
       if (st.empty()) break;
-      node = (int)st.pop().x;
+      node = (int)st.pop1();
     }
   }
   return false;
+}
+
+// Measured on C3 (profiles/r01_sweep_boxtest.txt): parking leaves pays for terminate-on-first-hit
+// rays (k_shadow 1.60 -> 0.89 ms: nothing is lost by testing late) and costs closest-hit rays
+// 10 % (k_trace 7.94 -> 8.78 ms: the per-step warp vote outweighs the fuller triangle tests).
+template <class Stack, bool ANY, bool COUNT>
+RT_HD bool trace_bvh2(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
+                      TravCounters* cnt) {
+  if (b.ntri == 0) return false;
+  if (b.ntri == 1) return test_leaf_tri<ANY, COUNT>(b, 0, r, tmin, inst, best, cnt);
+  if (ANY) return trace_bvh2_parked<Stack, ANY, COUNT>(b, r, tmin, inst, best, st, cnt);
+  return trace_bvh2_direct<Stack, ANY, COUNT>(b, r, tmin, inst, best, st, cnt);
 }
 
 // ---- compressed 8-wide BVH --------------------------------------------------------------
@@ -426,6 +498,8 @@ struct ArrayStack {
   RT_HD bool empty() const { return sp == 0; }
   RT_HD void push(uint2 v) { if (sp < N) e[sp++] = v; }
   RT_HD uint2 pop() { return e[--sp]; }
+  RT_HD void push1(uint32_t v) { if (sp < N) e[sp++] = make_uint2(v, 0u); }
+  RT_HD uint32_t pop1() { return e[--sp].x; }
 };
 
 }  // namespace rt

@@ -35,9 +35,11 @@ constexpr int STACK_LOCAL = 56;  // overflow entries in local memory
 
 // Traversal stack: the first STACK_SM entries live in shared memory (column per thread,
 // bank-conflict free), the rarely used rest in local memory.
+// The overflow array is a separate local array the struct only points to: with the array inside
+// the struct the compiler kept the whole struct, stack pointer included, in local memory.
 struct HybridStack {
   uint2* sm;      // &smem[threadIdx.x], stride blockDim.x
-  uint2 loc[STACK_LOCAL];
+  uint2* loc;     // STACK_LOCAL entries of thread-local memory
   int sp;
   __device__ __forceinline__ void reset() { sp = 0; }
   __device__ __forceinline__ bool empty() const { return sp == 0; }
@@ -196,8 +198,10 @@ __global__ void RT_TRACE_BOUNDS
             unsigned long long* __restrict__ stats64, int refill_thresh, int tri_thresh,
             const uint32_t* __restrict__ perm) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  uint2 stack_loc[STACK_LOCAL];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
+  st.loc = stack_loc;
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NRAY];
 #ifdef RT_WITH_PERSIST
@@ -325,8 +329,10 @@ __global__ void RT_TRACE_BOUNDS
              float4* __restrict__ sample, unsigned long long* __restrict__ stats64, int refill_thresh,
              int tri_thresh) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  uint2 stack_loc[STACK_LOCAL];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
+  st.loc = stack_loc;
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NSHADOW];
 #ifdef RT_WITH_PERSIST
@@ -418,8 +424,10 @@ __global__ void RT_TRACE_BOUNDS
                  uint32_t* __restrict__ qDiff, uint32_t* __restrict__ qSpec, rt_hit* __restrict__ primary,
                  unsigned long long* __restrict__ stats64, int refill_min, int tri_min, const uint32_t* __restrict__ perm) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  uint2 stack_loc[STACK_LOCAL];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
+  st.loc = stack_loc;
   TravCounters tc{0ull, 0ull};
   const WaveTraceSource src{rayO, rayD, perm};
   const WaveTraceSink sink{scene, U, cnt, rayO, perm, hits, qMiss, qDiff, qSpec, primary};
@@ -444,8 +452,10 @@ __global__ void RT_TRACE_BOUNDS
     k_shadow_wave(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
                   float4* __restrict__ sample, unsigned long long* __restrict__ stats64, int refill_min, int tri_min) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  uint2 stack_loc[STACK_LOCAL];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
+  st.loc = stack_loc;
   TravCounters tc{0ull, 0ull};
   const WaveShadowSource src{U, shadowQ};
   const ShadowSink sink{U, shadowQ, sample};
@@ -572,8 +582,10 @@ __global__ void __launch_bounds__(TRACE_THREADS)
     k_trace_batch(SceneDev scene, uint64_t n, const float* __restrict__ o, const float* __restrict__ d, float tmin,
                   float tmax, rt_hit* __restrict__ out, unsigned long long* __restrict__ stats64) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  uint2 stack_loc[STACK_LOCAL];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
+  st.loc = stack_loc;
   TravCounters tc{0ull, 0ull};
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
     HitRec h;

@@ -66,7 +66,17 @@ struct RayObj {
   uint32_t octinv4; // (dx>=0?4:0 | dy>=0?2:0 | dz>=0?1:0) replicated in 4 bytes
 };
 
-RT_HD float sel3(f3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+// component k of v for a per-ray k.  On the device two byte-permutes with computed selectors:
+// the ternary form compiled into divergent branches (7 BSSY/BRA/BSYNC blocks per triangle test).
+RT_HD float sel3(f3 v, int k) {
+#if defined(__CUDA_ARCH__)
+  const uint32_t s1 = 0x3210u + (uint32_t)(k & 1) * 0x4444u;   // k == 1: take y
+  const uint32_t s2 = 0x3210u + (uint32_t)(k >> 1) * 0x4444u;  // k == 2: take z
+  return __uint_as_float(__byte_perm(__byte_perm(__float_as_uint(v.x), __float_as_uint(v.y), s1), __float_as_uint(v.z), s2));
+#else
+  return k == 0 ? v.x : (k == 1 ? v.y : v.z);
+#endif
+}
 
 RT_HD float safe_rcp_dir(float d) {
   float a = fabsf(d) > 1e-20f ? d : copysignf(1e-20f, d);

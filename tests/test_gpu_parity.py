@@ -164,6 +164,35 @@ def test_trace_rays_closest_and_any(gpu_rt, ob):
     sc.close()
 
 
+@pytest.mark.parametrize("accel", [0, 3])
+def test_axis_parallel_and_far_rays(gpu_rt, ob, accel):
+    """Box culling must stay conservative where the slab arithmetic degenerates: directions with
+    exactly-zero components (1/d clamped), origins lying on box planes, origins far from the
+    scene.  Closest hits must equal the oracle's brute force bit for bit."""
+    rt = gpu_rt
+    inputs = scenes.c3_scene(rt, level=3, sky_size=8)
+    rng = np.random.default_rng(11)
+    n = 6000
+    axes = np.eye(3, dtype=np.float32)
+    d = np.concatenate([axes[rng.integers(0, 3, n)] * rng.choice([-1.0, 1.0], (n, 1)).astype(np.float32),      # axis parallel
+                        np.stack([rng.normal(size=n), np.zeros(n), rng.normal(size=n)], 1).astype(np.float32),  # one zero component
+                        rng.normal(size=(n, 3)).astype(np.float32)])
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    tgt = rng.normal(0, 1.2, (3 * n, 3)).astype(np.float32) + np.array([0, 0.5, 2.5], np.float32)
+    dist = np.concatenate([rng.uniform(3, 12, 2 * n), rng.uniform(2000, 9000, n)]).astype(np.float32)[:, None]
+    o = (tgt - d * dist).astype(np.float32)
+    o[:n:3] = np.round(o[:n:3], 0)          # many origins with integer coordinates (on box planes of the cube-ish teapot lid)
+    sc = rt.Scene(inputs, device_id=0, accel=accel)
+    osc = ob.OracleScene(inputs)
+    a, b = sc.trace_rays(o, d, 0.001, 10000.0), osc.trace_rays(o, d, 0.001, 10000.0, brute=True)
+    for f in ("instance", "primitive", "t", "u", "v"):
+        assert np.array_equal(a[f], b[f]), f
+    assert (a["instance"] != rt.MISS).mean() > 0.1
+    with pytest.raises(rt.RtError):
+        sc.trace_rays(o[:4], d[:4], -1.0, 10.0)   # traceRayEXT requires tmin >= 0
+    sc.close()
+
+
 def test_edge_cases(gpu_rt, ob):
     rt = gpu_rt
     cv, ci = scenes.unit_cube()
@@ -201,7 +230,7 @@ def test_error_paths(gpu_rt):
 
 def test_sort_pairs_matches_numpy(gpu_rt):
     rng = np.random.default_rng(3)
-    for n in (1, 31, 4096, 4097, 300001):
+    for n in (1, 31, 4096, 4097, 300001, 3000001):   # the last one: more tiles than resident blocks
         k = rng.integers(0, 2 ** 63, n, dtype=np.uint64)
         k[::7] = k[0]  # duplicates: stability matters
         v = np.arange(n, dtype=np.uint32)

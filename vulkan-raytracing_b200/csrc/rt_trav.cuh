@@ -100,7 +100,9 @@ RT_HD RayObj ray_setup(f3 o, f3 d) {
   r.Sy = sel3(d, ky) / dz;
   r.Sz = 1.0f / dz;
   r.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
-  r.octinv4 = ((d.x >= 0.0f ? 4u : 0u) | (d.y >= 0.0f ? 2u : 0u) | (d.z >= 0.0f ? 1u : 0u)) * 0x01010101u;
+  // signs taken from idir, the value the plane distances are multiplied with: for d = -0 the
+  // clamped reciprocal is negative while "d >= 0" would say positive
+  r.octinv4 = ((r.idir.x >= 0.0f ? 4u : 0u) | (r.idir.y >= 0.0f ? 2u : 0u) | (r.idir.z >= 0.0f ? 1u : 0u)) * 0x01010101u;
   return r;
 }
 
@@ -353,7 +355,7 @@ RT_HD uint32_t wide_node_test(const float4 n0, const uint4 n1, const uint4 n2, c
               bnz = fmaf(-cell, fabsf(az), (bz - Az) * kn);
   const float bfx = fmaf(cell, fabsf(ax), (bx - Ax) * kf), bfy = fmaf(cell, fabsf(ay), (by - Ay) * kf),
               bfz = fmaf(cell, fabsf(az), (bz - Az) * kf);
-  const bool px = r.d.x >= 0.0f, py = r.d.y >= 0.0f, pz = r.d.z >= 0.0f;
+  const bool px = r.idir.x >= 0.0f, py = r.idir.y >= 0.0f, pz = r.idir.z >= 0.0f;  // same rule as octinv4
   uint32_t hitmask = 0;
 #pragma unroll
   for (int half = 0; half < 2; half++) {

@@ -61,6 +61,9 @@ def parse_args():
     ap.add_argument("--accel", type=int, default=0, help="RT_ACCEL_*: 0 = default (binary BVH), 3 = compressed 8-wide BVH")
     ap.add_argument("--flags", type=int, default=0, help="extra rt_scene_desc flags, e.g. 16 = RT_FLAG_NO_REFINE")
     ap.add_argument("--sky", type=int, default=2048, help="procedural skybox face size")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: 'peer' = every rank's resolve kernel stores its tiles into rank 0's frame over NVLink "
+                         "(falls back to 'nccl' if the frame cannot be shared); 'nccl' = gather collective + de-interleave")
     return ap.parse_args()
 
 
@@ -226,28 +229,86 @@ def main():
     scene.set_stream(torch.cuda.current_stream().cuda_stream)
     cam = scenes.c5_camera(rt) if wl.startswith("c5") else rt.CameraVectors.default()
     sharded = world > 1
-    p_dev = rt.FrameParams.make(W, H, depth, spp, output_location=rt.LOCATION_DEVICE,
-                                shard_index=rank if sharded else 0, shard_count=world if sharded else 1)
-    npix_local = int(rt.rt_lib().rt_frame_shard_pixels(C.byref(p_dev))) if sharded else W * H
-    local = torch.zeros((npix_local, 4), dtype=torch.uint8, device=dev)
-    gathered = torch.zeros((world, npix_local, 4), dtype=torch.uint8, device=dev) if (sharded and rank == 0) else None
-    frame = torch.zeros((H, W, 4), dtype=torch.uint8, device=dev) if rank == 0 else None
-    host = torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+    p_compact = rt.FrameParams.make(W, H, depth, spp, output_location=rt.LOCATION_DEVICE,
+                                    shard_index=rank if sharded else 0, shard_count=world if sharded else 1)
+    npix_local = int(rt.rt_lib().rt_frame_shard_pixels(C.byref(p_compact))) if sharded else W * H
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
     launches = {"n": 0}
+    host = torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+
+    # ---- how the tiles reach rank 0 -----------------------------------------------------------------
+    gather, peer = "none", None
+    if sharded:
+        gather = args.gather
+        if gather == "peer":   # rank 0 owns the frame, everybody else maps it (CUDA IPC, NVLink peer stores)
+            ok = torch.ones(1, device=dev)
+            handle = torch.zeros(64, dtype=torch.uint8, device=dev)
+            if rank == 0:
+                try:
+                    peer = rt.PeerFrame.create(local_rank, W * H * 4)
+                    handle.copy_(torch.frombuffer(bytearray(peer.handle_bytes()), dtype=torch.uint8))
+                except rt.RtError as e:
+                    sys.stderr.write(f"peer frame: {e}\n")
+                    ok.zero_()
+            dist.broadcast(handle, src=0)
+            if rank != 0:
+                try:
+                    peer = rt.PeerFrame.open(local_rank, handle.cpu().numpy().tobytes(), W * H * 4)
+                except rt.RtError as e:
+                    sys.stderr.write(f"rank {rank} peer frame: {e}\n")
+                    ok.zero_()
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if float(ok.item()) == 0.0:
+                if peer is not None:
+                    peer.release()
+                    peer = None
+                gather = "nccl"
+    if gather == "peer":
+        p_dev = p_compact.copy()
+        p_dev.shard_layout = rt.SHARD_IN_FRAME
+        frame = torch.as_tensor(peer, device=dev).view(H, W, 4) if rank == 0 else None
+        local = gathered = None
+    else:
+        p_dev = p_compact
+        local = torch.zeros((npix_local, 4), dtype=torch.uint8, device=dev)
+        gathered = torch.zeros((world, npix_local, 4), dtype=torch.uint8, device=dev) if (sharded and rank == 0) else None
+        frame = torch.zeros((H, W, 4), dtype=torch.uint8, device=dev) if (sharded and rank == 0) else None
+
+    def nccl_step(p, loc, gat, frm):
+        scene.render_into(cam, p, loc.data_ptr())
+        launches["n"] += scene.stats()["kernel_launches"]
+        dist.gather(loc, [gat[i] for i in range(world)] if rank == 0 else None, dst=0)
+        if rank == 0:
+            scene.assemble_shards(p, gat.data_ptr(), frm.data_ptr())
+            launches["n"] += 1
 
     def step(to_host):
-        scene.render_into(cam, p_dev, local.data_ptr())
-        launches["n"] += scene.stats()["kernel_launches"]
-        if sharded:
-            dist.gather(local, [gathered[i] for i in range(world)] if rank == 0 else None, dst=0)
-            if rank == 0:
-                scene.assemble_shards(p_dev, gathered.data_ptr(), frame.data_ptr())
-                launches["n"] += 1
+        if gather == "peer":
+            scene.render_into(cam, p_dev, peer.ptr)   # returns once this rank's stores have completed
+            launches["n"] += scene.stats()["kernel_launches"]
+            dist.barrier()                            # ... and now everybody's have
+        elif gather == "nccl":
+            nccl_step(p_dev, local, gathered, frame)
+        else:
+            scene.render_into(cam, p_dev, local.data_ptr())
+            launches["n"] += scene.stats()["kernel_launches"]
         if to_host and rank == 0:
             src = frame if sharded else local.view(H, W, 4)
             host.copy_(src, non_blocking=True)
             torch.cuda.current_stream().synchronize()
+
+    gather_verified = None
+    if gather == "peer":   # once, outside the timed region: the collective path must give the same frame
+        step(False)
+        loc = torch.zeros((npix_local, 4), dtype=torch.uint8, device=dev)
+        gat = torch.zeros((world, npix_local, 4), dtype=torch.uint8, device=dev) if rank == 0 else None
+        frm = torch.zeros((H, W, 4), dtype=torch.uint8, device=dev) if rank == 0 else None
+        nccl_step(p_compact, loc, gat, frm)
+        torch.cuda.synchronize()
+        if rank == 0:
+            gather_verified = bool(torch.equal(frm, frame))
+        del loc, gat, frm
+        torch.cuda.empty_cache()
 
     def timed(to_host, steps):
         ms, rays = 0.0, 0
@@ -286,11 +347,14 @@ def main():
 
     # counting frame (outside the timed region): exact node / triangle-test counts
     scene.set_counting(True)
-    scene.render_into(cam, p_dev, local.data_ptr())
+    scene.render_into(cam, p_dev, peer.ptr if gather == "peer" else local.data_ptr())
     st_count = scene.stats()
     scene.set_counting(False)
     fp32 = rt.measure_fp32_tflops(local_rank) if rank == 0 else 0.0
     if rank != 0:
+        if peer is not None:
+            torch.cuda.synchronize()
+            peer.release()          # peers unmap before the owner frees
         if world > 1:
             dist.barrier()
             dist.destroy_process_group()
@@ -311,6 +375,14 @@ def main():
                      "shade_raygen_resolve": round(st_last["shade_ms"], 4), "frame_in_library": round(st_last["frame_ms"], 4)},
         "bvh": {"nodes": st_last["bvh_nodes"], "bytes": st_last["bvh_bytes"]},
     }
+    if sharded:
+        out["gather"] = {
+            "peer": "k_resolve of every rank stores its tiles into rank 0's frame (CUDA IPC mapping, NVLink peer stores), "
+                    "then one barrier; no gather collective, no de-interleave pass",
+            "nccl": "torch.distributed.gather (NCCL) of the compact tile buffers + rt_assemble_shards"}[gather]
+        out["gather_mode"] = gather
+        if gather_verified is not None:
+            out["gather_equals_nccl_path"] = gather_verified
     out["roofline"] = roofline(st_count, st_last["trace_ms"] + st_last["shadow_ms"], st_last["frame_ms"], hbm, hbm_src, fp32,
                                npix_local)
     if world == 1 and not args.no_cpu_baseline:
@@ -320,7 +392,10 @@ def main():
                                "ms_per_sample": round(ms, 1)}
     print(json.dumps(out))
     if world > 1:
-        dist.barrier()
+        dist.barrier()              # the peers have unmapped the frame
+        if peer is not None:
+            del frame
+            peer.release()
         dist.destroy_process_group()
     return 0
 

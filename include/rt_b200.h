@@ -119,7 +119,14 @@ typedef struct rt_camera {
  * with (tile_index % n) == s, using GLOBAL pixel coordinates and the GLOBAL
  * launch size for ray generation, and writes them compactly, tile after tile
  * (each tile_w*tile_h pixels row-major, edge tiles padded) in increasing
- * tile_index order.  shard_count <= 1 renders the full frame, row-major. */
+ * tile_index order.  shard_count <= 1 renders the full frame, row-major.
+ * shard_layout = RT_SHARD_IN_FRAME instead makes the shard store its pixels at
+ * their final row-major position of a full width x height frame (device
+ * pointer; pixels of other shards are left untouched).  That frame may live on
+ * another GPU of the box (rt_peer_frame_*): every GPU then stores its tiles
+ * straight into the gathering GPU's frame over NVLink and the per-frame gather
+ * collective and the de-interleave pass disappear. */
+enum { RT_SHARD_COMPACT = 0, RT_SHARD_IN_FRAME = 1 };
 typedef struct rt_frame_params {
   uint32_t width, height;
   uint32_t max_bounce_count;      /* MAX_BOUNCE_COUNT, config.h:26 */
@@ -130,6 +137,7 @@ typedef struct rt_frame_params {
   uint32_t output_location;       /* RT_LOCATION_* */
   uint32_t shard_index, shard_count;
   uint32_t tile_w, tile_h;        /* 0 = default 64x64 */
+  uint32_t shard_layout;          /* RT_SHARD_*; RT_SHARD_IN_FRAME needs RT_LOCATION_DEVICE */
 } rt_frame_params;
 
 /* Hit record of one closest-hit trace (what the driver hands shader.rchit:
@@ -202,6 +210,21 @@ uint64_t rt_frame_shard_pixels(const rt_frame_params* params);
  * long (device pointer); frame_out = width*height pixels (device pointer). */
 int rt_assemble_shards(void* scene, const rt_frame_params* params, const void* gathered,
                        void* frame_out);
+
+/* Frame buffer that other processes of the same box (one per GPU) can store into:
+ * the tile gather of the multi-GPU path without a collective.  The gathering
+ * process creates the frame and hands the 64-byte handle to its peers by any
+ * means (torch.distributed broadcast in bench.py); each peer opens it once and
+ * passes the returned device pointer as rgba_out of rt_render_frame with
+ * shard_layout = RT_SHARD_IN_FRAME.  rt_render_frame returns after the stores
+ * have completed; a barrier between the processes then makes the frame
+ * readable on the owner.  (CUDA IPC + NVLink peer access underneath; there is
+ * no Vulkan counterpart, the reference is single-GPU.) */
+typedef struct rt_ipc_handle { unsigned char opaque[64]; } rt_ipc_handle;
+int rt_peer_frame_create(int device_id, uint64_t bytes, void** frame_out, rt_ipc_handle* handle_out);
+int rt_peer_frame_open(int device_id, const rt_ipc_handle* handle, void** frame_out);
+int rt_peer_frame_close(int device_id, void* frame);     /* peer side */
+int rt_peer_frame_destroy(int device_id, void* frame);   /* owner side */
 
 /* --- parity / measurement exports --------------------------------------------- */
 /* Primary-ray hit records of a frame: width*height*samples_per_pixel records,

@@ -263,6 +263,46 @@ def test_sharded_frame_is_bit_identical(gpu_rt):
     sc.close()
 
 
+def test_shards_stored_in_frame_equal_the_full_frame(gpu_rt):
+    """RT_SHARD_IN_FRAME (the collective-free gather): every shard stores its tiles at their final
+    position of one frame; pixels of the other shards stay untouched; a frame created by
+    rt_peer_frame_create is an ordinary device buffer for its owner."""
+    import torch
+    rt = gpu_rt
+    inputs = scenes.smoke_scene(rt)
+    sc = rt.Scene(inputs, device_id=0)
+    cam = rt.CameraVectors.default()
+    for fmt, dt, px in ((rt.FORMAT_RGBA8, torch.uint8, 4), (rt.FORMAT_RGBA32F, torch.float32, 16)):
+        p = rt.FrameParams.make(200, 136, 5, 2, output_format=fmt, tile_w=32, tile_h=16)
+        full = sc.render(cam, p)
+        n = 3
+        q = p.copy()
+        q.shard_count, q.output_location, q.shard_layout = n, rt.LOCATION_DEVICE, rt.SHARD_IN_FRAME
+        assert int(rt.rt_lib().rt_frame_output_bytes(q)) == 200 * 136 * px
+        pf = rt.PeerFrame.create(0, 200 * 136 * px)
+        assert len(pf.handle_bytes()) == 64 and any(pf.handle_bytes())
+        frame = torch.as_tensor(pf, device="cuda:0").view(dt).view(136, 200, 4)
+        frame.fill_(7)
+        seen = np.zeros((136, 200), bool)
+        for s in range(n):
+            q.shard_index = s
+            sc.render_into(cam, q, pf.ptr)
+            now = frame.cpu().numpy()
+            ty, tx = np.mgrid[0:136, 0:200]
+            mine = ((ty // 16) * ((200 + 31) // 32) + tx // 32) % n == s
+            seen |= mine
+            assert np.array_equal(now[seen], full[seen])
+            assert np.all(now[~seen] == 7)
+        assert seen.all()
+        del frame
+        pf.release()
+    # host output of a partial frame is refused
+    bad = rt.FrameParams.make(64, 64, 1, 1, shard_count=2, shard_layout=rt.SHARD_IN_FRAME)
+    with pytest.raises(rt.RtError):
+        sc.render(cam, bad)
+    sc.close()
+
+
 def test_full_size_properties(gpu_rt, ob):
     """BASELINE C3 size (3840x2160, depth 8): size-independent checks — a centred crop rendered by
     the oracle matches the same pixels of the full CUDA frame exactly, and ray counts are consistent."""

@@ -42,7 +42,7 @@ def test_rt_host_exports_every_declared_symbol(rt):
 
 def test_struct_layouts_match_header(rt):
     assert C.sizeof(rt.MeshDesc) == 32 and C.sizeof(rt.InstanceDesc) == 56
-    assert C.sizeof(rt.CameraVectors) == 48 and C.sizeof(rt.FrameParams) == 56 and C.sizeof(rt.Hit) == 20
+    assert C.sizeof(rt.CameraVectors) == 48 and C.sizeof(rt.FrameParams) == 60 and C.sizeof(rt.Hit) == 20 and C.sizeof(rt.IpcHandle) == 64
     assert rt.HIT_DTYPE.itemsize == 20
 
 

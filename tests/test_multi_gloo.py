@@ -72,3 +72,49 @@ def test_two_rank_tile_sharding_matches_full_frame(rt, ob, tmp_path, w, h, tw, t
     frame = np.load(out)
     ref = ob.OracleScene(scenes.smoke_scene(rt)).render(rt.CameraVectors.default(), rt.FrameParams.make(w, h, 4, 2))["rgba8"]
     assert np.array_equal(frame, ref)
+
+
+def in_frame_worker(rank, world, port, w, h, tw, th, frame_path):
+    """RT_SHARD_IN_FRAME on CPU: every rank stores its tiles straight into one shared frame (a memmap stands in for
+    the peer-mapped device frame), in the row-by-row order of k_resolve, then a barrier; no gather."""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import __graft_entry__ as graft
+    rt = graft.load_package()
+    import emu_binding as emu
+    import scenes
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    inputs = scenes.smoke_scene(rt)
+    cam = rt.CameraVectors.default()
+    p = rt.FrameParams.make(w, h, 4, 2, tile_w=tw, tile_h=th, shard_index=rank, shard_count=world)
+    full = emu.EmuScene(inputs, 0).render(cam, p)["rgba8"]
+    frame = np.memmap(frame_path, dtype=np.uint8, mode="r+", shape=(h, w, 4))
+    tiles_x = (w + tw - 1) // tw
+    tiles = tiles_x * ((h + th - 1) // th)
+    n_local = (tiles - rank + world - 1) // world if tiles > rank else 0
+    for q in range(n_local * tw * th):          # q walks each tile row-major, like the in-frame branch of k_resolve
+        lt, inn = divmod(q, tw * th)
+        ty, tx = divmod(inn, tw)
+        pslot = lt * tw * th + ((ty // 4) * (tw // 8) + tx // 8) * 32 + (ty % 4) * 8 + tx % 8
+        ok, x, y = emu.slot_to_pixel(p, pslot)  # the slot whose samples belong to that pixel
+        tile = lt * world + rank
+        assert (x, y) == ((tile % tiles_x) * tw + tx, (tile // tiles_x) * th + ty)
+        if ok:
+            frame[y, x] = full[y, x]
+    frame.flush()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_ranks_store_into_one_frame(rt, ob, tmp_path):
+    import scenes
+    w, h, tw, th = 100, 68, 32, 16
+    path = str(tmp_path / "frame.bin")
+    np.full((h, w, 4), 7, np.uint8).tofile(path)
+    port = 31500 + (os.getpid() % 2000)
+    mp.spawn(in_frame_worker, args=(2, port, w, h, tw, th, path), nprocs=2, join=True)
+    frame = np.fromfile(path, np.uint8).reshape(h, w, 4)
+    ref = ob.OracleScene(scenes.smoke_scene(rt)).render(rt.CameraVectors.default(), rt.FrameParams.make(w, h, 4, 2))["rgba8"]
+    assert np.array_equal(frame, ref)

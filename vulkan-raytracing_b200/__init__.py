@@ -30,6 +30,7 @@ HOST_LIB_PATH = os.path.join(_HERE, "librt_host.so")
 TYPE_DIFFUSE, TYPE_MIRROR, TYPE_REFRACTIVE = 0, 1, 2
 FORMAT_RGBA8, FORMAT_RGBA32F = 0, 1
 LOCATION_HOST, LOCATION_DEVICE = 0, 1
+SHARD_COMPACT, SHARD_IN_FRAME = 0, 1
 ACCEL_DEFAULT, ACCEL_BVH2, ACCEL_BRUTE, ACCEL_WIDE8 = 0, 1, 2, 3
 FLAG_NO_REFINE = 0x10
 MISS = 0xFFFFFFFF
@@ -80,12 +81,12 @@ class FrameParams(C.Structure):
                 ("samples_per_pixel", C.c_uint32), ("light_position", C.c_float * 3),
                 ("light_intensity", C.c_float), ("output_format", C.c_uint32),
                 ("output_location", C.c_uint32), ("shard_index", C.c_uint32), ("shard_count", C.c_uint32),
-                ("tile_w", C.c_uint32), ("tile_h", C.c_uint32)]
+                ("tile_w", C.c_uint32), ("tile_h", C.c_uint32), ("shard_layout", C.c_uint32)]
 
     @staticmethod
     def make(width=800, height=600, max_bounce_count=63, samples_per_pixel=4, light_position=(5, 5, 5),
              light_intensity=1.0, output_format=FORMAT_RGBA8, output_location=LOCATION_HOST, shard_index=0,
-             shard_count=1, tile_w=0, tile_h=0) -> "FrameParams":
+             shard_count=1, tile_w=0, tile_h=0, shard_layout=SHARD_COMPACT) -> "FrameParams":
         p = FrameParams()
         p.width, p.height = int(width), int(height)
         p.max_bounce_count, p.samples_per_pixel = int(max_bounce_count), int(samples_per_pixel)
@@ -94,12 +95,17 @@ class FrameParams(C.Structure):
         p.output_format, p.output_location = int(output_format), int(output_location)
         p.shard_index, p.shard_count = int(shard_index), int(shard_count)
         p.tile_w, p.tile_h = int(tile_w), int(tile_h)
+        p.shard_layout = int(shard_layout)
         return p
 
     def copy(self) -> "FrameParams":
         q = FrameParams()
         C.memmove(C.byref(q), C.byref(self), C.sizeof(FrameParams))
         return q
+
+
+class IpcHandle(C.Structure):
+    _fields_ = [("opaque", C.c_uint8 * 64)]
 
 
 class Hit(C.Structure):
@@ -347,6 +353,10 @@ def rt_lib():
         L.rt_frame_shard_pixels.restype = C.c_uint64
         L.rt_frame_shard_pixels.argtypes = [C.POINTER(FrameParams)]
         L.rt_assemble_shards.argtypes = [C.c_void_p, C.POINTER(FrameParams), C.c_void_p, C.c_void_p]
+        L.rt_peer_frame_create.argtypes = [C.c_int, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(IpcHandle)]
+        L.rt_peer_frame_open.argtypes = [C.c_int, C.POINTER(IpcHandle), C.POINTER(C.c_void_p)]
+        L.rt_peer_frame_close.argtypes = [C.c_int, C.c_void_p]
+        L.rt_peer_frame_destroy.argtypes = [C.c_int, C.c_void_p]
         L.rt_primary_hits.argtypes = [C.c_void_p, C.POINTER(CameraVectors), C.POINTER(FrameParams), C.c_void_p]
         L.rt_trace_rays.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int,
                                     C.c_void_p]
@@ -436,6 +446,44 @@ class Scene:
         s = Stats()
         _check(rt_lib().rt_get_stats(self._h, C.byref(s)))
         return s.as_dict()
+
+
+class PeerFrame:
+    """A frame buffer the other ranks of the box store their tiles into (rt_peer_frame_*).
+
+    Owner: PeerFrame.create(device, nbytes) -> .handle_bytes() goes to the peers.
+    Peer:  PeerFrame.open(device, handle_bytes).  `.ptr` is the device address to pass as the
+    output of Scene.render_into with shard_layout=SHARD_IN_FRAME."""
+
+    def __init__(self, device_id: int, ptr: int, nbytes: int, owner: bool, handle: "IpcHandle | None"):
+        self.device_id, self.ptr, self.nbytes, self.owner, self._handle = device_id, ptr, nbytes, owner, handle
+
+    @staticmethod
+    def create(device_id: int, nbytes: int) -> "PeerFrame":
+        d, h = C.c_void_p(), IpcHandle()
+        _check(rt_lib().rt_peer_frame_create(device_id, nbytes, C.byref(d), C.byref(h)))
+        return PeerFrame(device_id, d.value, nbytes, True, h)
+
+    @staticmethod
+    def open(device_id: int, handle_bytes: bytes, nbytes: int = 0) -> "PeerFrame":
+        h = IpcHandle()
+        C.memmove(C.byref(h), bytes(handle_bytes), 64)
+        d = C.c_void_p()
+        _check(rt_lib().rt_peer_frame_open(device_id, C.byref(h), C.byref(d)))
+        return PeerFrame(device_id, d.value, nbytes, False, None)
+
+    def handle_bytes(self) -> bytes:
+        return bytes(self._handle.opaque)
+
+    @property
+    def __cuda_array_interface__(self):   # lets torch / cupy view the frame as uint8[nbytes]
+        return {"shape": (self.nbytes,), "typestr": "|u1", "data": (self.ptr, False), "version": 2}
+
+    def release(self):
+        if self.ptr:
+            L = rt_lib()
+            _check((L.rt_peer_frame_destroy if self.owner else L.rt_peer_frame_close)(self.device_id, C.c_void_p(self.ptr)))
+            self.ptr = 0
 
 
 def measure_fp32_tflops(device_id: int = 0) -> float:

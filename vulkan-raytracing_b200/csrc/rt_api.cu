@@ -148,6 +148,10 @@ static int fill_uniforms(const rt_camera* cam, const rt_frame_params* p, FrameUn
   if (U.shard_index >= U.shard_count) return fail(RT_ERR_INVALID_ARGUMENT, "shard_index >= shard_count");
   const uint32_t tiles = U.tiles_x * U.tiles_y;
   U.n_local_tiles = tiles > U.shard_index ? (tiles - U.shard_index + U.shard_count - 1) / U.shard_count : 0;
+  if (p->shard_layout > RT_SHARD_IN_FRAME) return fail(RT_ERR_INVALID_ARGUMENT, "bad shard_layout");
+  if (p->shard_layout == RT_SHARD_IN_FRAME && p->output_location != RT_LOCATION_DEVICE)
+    return fail(RT_ERR_INVALID_ARGUMENT, "RT_SHARD_IN_FRAME writes into a device frame (RT_LOCATION_DEVICE)");
+  U.in_frame = p->shard_layout == RT_SHARD_IN_FRAME ? 1u : 0u;
   return RT_OK;
 }
 
@@ -292,7 +296,8 @@ uint64_t rt_frame_shard_pixels(const rt_frame_params* p) { return p ? shard_pixe
 
 uint64_t rt_frame_output_bytes(const rt_frame_params* p) {
   if (!p) return 0;
-  const uint64_t px = (p->shard_count > 1) ? shard_pixels(p) : (uint64_t)p->width * p->height;
+  const bool compact = p->shard_count > 1 && p->shard_layout != RT_SHARD_IN_FRAME;
+  const uint64_t px = compact ? shard_pixels(p) : (uint64_t)p->width * p->height;
   return px * (p->output_format == RT_FORMAT_RGBA8 ? 4 : 16);
 }
 
@@ -334,6 +339,52 @@ int rt_render_frame(void* scene, const rt_camera* cam, const rt_frame_params* p,
   Scene* s = (Scene*)scene;
   if (!s || !rgba_out) return fail(RT_ERR_INVALID_ARGUMENT, "null scene or output");
   return render_common(s, cam, p, rgba_out, nullptr);
+}
+
+// ---- frame buffers other processes can store into (CUDA IPC over NVLink peer access) ----------
+int rt_peer_frame_create(int device_id, uint64_t bytes, void** frame_out, rt_ipc_handle* handle_out) {
+  if (!frame_out || !handle_out || bytes == 0) return fail(RT_ERR_INVALID_ARGUMENT, "null argument or empty frame");
+  static_assert(sizeof(cudaIpcMemHandle_t) <= sizeof(rt_ipc_handle), "handle size");
+  if (rt_device_count() < 1) return fail(RT_ERR_NO_DEVICE, "no CUDA device");
+  RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
+  void* d = nullptr;
+  RT_CUDA_TRY(cudaMalloc(&d, bytes), g_err);
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, d);
+  if (e != cudaSuccess) {
+    cudaFree(d);
+    return fail(RT_ERR_CUDA, std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e));
+  }
+  std::memset(handle_out, 0, sizeof *handle_out);
+  std::memcpy(handle_out->opaque, &h, sizeof h);
+  *frame_out = d;
+  return RT_OK;
+}
+
+int rt_peer_frame_open(int device_id, const rt_ipc_handle* handle, void** frame_out) {
+  if (!handle || !frame_out) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  if (rt_device_count() < 1) return fail(RT_ERR_NO_DEVICE, "no CUDA device");
+  RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle->opaque, sizeof h);
+  void* d = nullptr;
+  RT_CUDA_TRY(cudaIpcOpenMemHandle(&d, h, cudaIpcMemLazyEnablePeerAccess), g_err);
+  *frame_out = d;
+  return RT_OK;
+}
+
+int rt_peer_frame_close(int device_id, void* frame) {
+  if (!frame) return RT_OK;
+  RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
+  RT_CUDA_TRY(cudaIpcCloseMemHandle(frame), g_err);
+  return RT_OK;
+}
+
+int rt_peer_frame_destroy(int device_id, void* frame) {
+  if (!frame) return RT_OK;
+  RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
+  RT_CUDA_TRY(cudaFree(frame), g_err);
+  return RT_OK;
 }
 
 int rt_assemble_shards(void* scene, const rt_frame_params* p, const void* gathered, void* frame_out) {

@@ -212,6 +212,9 @@ __global__ void RT_TRACE_BOUNDS
   } else
 #endif
   while (true) {
+    // (32 rays per pull also at the end of the queue: shrinking the last batches to even out the
+    // finishing times of the warps costs more in SIMD width than the shorter tail returns,
+    // profiles/r01_sweep_persistent.txt)
     uint32_t base = 0;
     if (lane_id() == 0) base = atomicAdd(&cnt[C_WTRACE], 32u);
     base = __shfl_sync(0xFFFFFFFFu, base, 0);
@@ -528,30 +531,49 @@ __global__ void __launch_bounds__(256)
 }
 
 // ---- resolve: color /= samples; imageStore ---------------------------------------------------
+// Three output layouts: full frame (row-major), compact shard (tile after tile, what the NCCL
+// gather ships) and shard-in-frame, where a shard stores its tiles at their final position in a
+// full frame that may sit in another GPU's memory.  For that one the threads walk the tiles row
+// by row, so a warp's store is one 128-byte run of a frame row (NVLink moves it as one packet
+// instead of four 32-byte ones); the samples are read through the 8x4 micro-block order they
+// were accumulated in.
 __global__ void __launch_bounds__(256) k_resolve(FrameUniforms U, uint32_t npix, const float4* __restrict__ sample,
                                                  void* __restrict__ out, uint32_t format) {
+  const uint32_t tile_px = U.tile_w * U.tile_h;
   for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x) {
-    uint32_t x, y;
-    const bool valid = slot_to_pixel(U, p, x, y);
+    uint32_t x, y, pslot = p;
+    bool valid;
+    size_t dst;
+    if (U.in_frame) {
+      const uint32_t lt = p / tile_px, in = p % tile_px;
+      const uint32_t tx = in % U.tile_w, ty = in / U.tile_w;
+      pslot = lt * tile_px + ((ty / 4) * (U.tile_w / 8) + tx / 8) * 32 + (ty % 4) * 8 + (tx % 8);
+      const uint32_t tile = lt * U.shard_count + U.shard_index;
+      x = (tile % U.tiles_x) * U.tile_w + tx;
+      y = (tile / U.tiles_x) * U.tile_h + ty;
+      valid = x < U.width && y < U.height;
+      if (!valid) continue;
+      dst = (size_t)y * U.width + x;
+    } else {
+      valid = slot_to_pixel(U, p, x, y);
+      if (U.shard_count <= 1) {
+        if (!valid) continue;
+        dst = (size_t)y * U.width + x;
+      } else {  // compact shard layout: tile after tile, each tile row-major
+        const uint32_t lt = p / tile_px;
+        const uint32_t tile = lt * U.shard_count + U.shard_index;
+        const uint32_t tx = x - (tile % U.tiles_x) * U.tile_w, ty = y - (tile / U.tiles_x) * U.tile_h;
+        dst = (size_t)lt * tile_px + (size_t)ty * U.tile_w + tx;
+      }
+    }
     float c[4] = {0.f, 0.f, 0.f, 0.f};
     if (valid) {
       for (uint32_t i = 0; i < U.spp; i++) {
-        const float4 s = sample[(size_t)p * U.spp + i];
+        const float4 s = sample[(size_t)pslot * U.spp + i];
         c[0] += s.x; c[1] += s.y; c[2] += s.z; c[3] += 1.0f;   // color += vec4(tmpColor, 1)
       }
       const float fs = (float)U.spp;
       c[0] = c[0] / fs; c[1] = c[1] / fs; c[2] = c[2] / fs; c[3] = c[3] / fs;
-    }
-    size_t dst;
-    if (U.shard_count <= 1) {
-      if (!valid) continue;
-      dst = (size_t)y * U.width + x;
-    } else {  // compact shard layout: tile after tile, each tile row-major
-      const uint32_t tile_px = U.tile_w * U.tile_h;
-      const uint32_t lt = p / tile_px;
-      const uint32_t tile = lt * U.shard_count + U.shard_index;
-      const uint32_t tx = x - (tile % U.tiles_x) * U.tile_w, ty = y - (tile / U.tiles_x) * U.tile_h;
-      dst = (size_t)lt * tile_px + (size_t)ty * U.tile_w + tx;
     }
     if (format == RT_FORMAT_RGBA8) {
       ((uint32_t*)out)[dst] = to_unorm8(c[0]) | (to_unorm8(c[1]) << 8) | (to_unorm8(c[2]) << 16) | (to_unorm8(c[3]) << 24);
@@ -621,6 +643,9 @@ struct FramePipeline {
   std::vector<uint32_t> h_cnt;
   cudaEvent_t ev[2] = {nullptr, nullptr};
   std::vector<cudaEvent_t> kev;  // per bounce: trace begin/end, shadow begin/end
+  uint32_t* h_alive = nullptr;   // pinned: rays entering bounce j, copied back without stalling the stream
+  size_t alive_cap = 0;
+  std::vector<cudaEvent_t> aev;  // aev[j]: h_alive[j] has landed
 };
 
 FramePipeline* pipeline_create() { return new FramePipeline(); }
@@ -640,6 +665,8 @@ void pipeline_destroy(FramePipeline* p) {
   cudaFree(p->cnt); cudaFree(p->stats64);
   for (auto& e : p->ev) if (e) cudaEventDestroy(e);
   for (auto& e : p->kev) cudaEventDestroy(e);
+  for (auto& e : p->aev) cudaEventDestroy(e);
+  if (p->h_alive) cudaFreeHost(p->h_alive);
   delete p;
 }
 
@@ -678,6 +705,17 @@ static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std:
     cudaEvent_t e;
     RT_CUDA_TRY(cudaEventCreate(&e), err);
     p->kev.push_back(e);
+  }
+  if (bounces + 2 > p->alive_cap) {
+    if (p->h_alive) cudaFreeHost(p->h_alive);
+    p->h_alive = nullptr;
+    p->alive_cap = bounces + 2;
+    RT_CUDA_TRY(cudaHostAlloc(&p->h_alive, p->alive_cap * sizeof(uint32_t), cudaHostAllocDefault), err);
+  }
+  while (p->aev.size() < bounces + 2) {
+    cudaEvent_t e;
+    RT_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), err);
+    p->aev.push_back(e);
   }
   return RT_OK;
 }
@@ -780,19 +818,22 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
       launches++;
       cur ^= 1;
       perm = nullptr;
-      // deep bounce limits (MAX_BOUNCE_COUNT 63): stop as soon as no ray survives
       if (sorting) {  // reorder the next bounce's rays; the count stays on the device
         int rc2 = sort_pairs_u32(p->sortK[0], p->sortK[1], p->sortV[0], p->sortV[1], p->cap, cn + C_NRAY, sort_bits, p->sortH, st, err);
         if (rc2 != RT_OK) return rc2;
         launches += sort_launches(sort_bits);
         perm = p->sortV[0];
       }
-      if (j >= 3) {
-        uint32_t alive = 0;
-        RT_CUDA_TRY(cudaMemcpyAsync(&alive, cn + C_NRAY, sizeof alive, cudaMemcpyDeviceToHost, st), err);
-        RT_CUDA_TRY(cudaStreamSynchronize(st), err);
-        if (alive == 0) break;
-      }
+      // Deep bounce limits (MAX_BOUNCE_COUNT 63): stop as soon as no ray survives.  The count
+      // travels to pinned memory behind the bounce; bounces 1-8 only look at counts
+      // that have already landed (no stall), deeper ones wait for theirs.
+      RT_CUDA_TRY(cudaMemcpyAsync(&p->h_alive[j + 1], cn + C_NRAY, sizeof(uint32_t), cudaMemcpyDeviceToHost, st), err);
+      RT_CUDA_TRY(cudaEventRecord(p->aev[j + 1], st), err);
+      if (j + 1 > 8) { RT_CUDA_TRY(cudaEventSynchronize(p->aev[j + 1]), err); }
+      bool dead = false;
+      for (uint32_t k = 1; k <= j + 1 && !dead; k++)
+        dead = cudaEventQuery(p->aev[k]) == cudaSuccess && p->h_alive[k] == 0u;
+      if (dead) break;
     }
   }
   if (rq.d_out) {

@@ -19,6 +19,7 @@ struct FrameUniforms {
   uint32_t tile_w, tile_h, tiles_x, tiles_y;
   uint32_t shard_index, shard_count;
   uint32_t n_local_tiles;          // tiles owned by this shard
+  uint32_t in_frame;               // resolve stores at final row-major positions (RT_SHARD_IN_FRAME)
 };
 
 // internal pixel slot -> global pixel coordinates; false for padding outside the frame

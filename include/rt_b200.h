@@ -187,6 +187,24 @@ int rt_scene_build(const rt_scene_desc* desc, void** out_scene);
 /* Per-frame instance transforms: the TLAS UPDATE of main.cpp:2836-2861, without
  * the blocking rebuild.  xforms12 = n_instances x 12 floats, row-major 3x4. */
 int rt_scene_set_transforms(void* scene, const float* xforms12, uint32_t n_instances);
+/* Per-instance materials.  The reference parses the .mtl
+ * files next to its meshes and then ignores them: every surface is shaded with
+ * the constants of shader.rgen:51-55 (kd, ka, ks, Iamb, index_of_refraction)
+ * and the exponent 100 of shader.rgen:125.  A scene starts with exactly those
+ * constants; this call replaces them per instance with Ka/Kd/Ks/Ns/Ni of a
+ * material.  At a front-facing diffuse hit the sample becomes
+ *   Iamb*ka + 0.9^i * I * (kd*max(0,N.L) + ks*max(0,N.H)^ns)   (unshadowed)
+ *   Iamb*ka                                                    (shadowed)
+ * and refraction uses ni instead of 1.52.  materials = n_instances records, or
+ * NULL to return to the reference constants (bit-identical to never calling). */
+typedef struct rt_material {
+  float ka[3];   /* ambient reflectance,  reference 0.1 0.3 0.1 */
+  float kd[3];   /* diffuse reflectance,  reference 0.2 1.0 0.2 */
+  float ks[3];   /* specular reflectance, reference 0.8 0.8 0.8 */
+  float ns;      /* specular exponent,    reference 100 */
+  float ni;      /* index of refraction,  reference 1.52 */
+} rt_material;
+int rt_scene_set_materials(void* scene, const rt_material* materials, uint32_t n_instances);
 /* main.cpp:2974-3062. */
 int rt_scene_destroy(void* scene);
 /* CUDA stream (cudaStream_t) all later work of this scene is issued on;

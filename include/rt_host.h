@@ -24,6 +24,19 @@ enum {
 const char* rth_last_error(void);
 void rth_free(void* p);
 
+/* Wavefront .mtl reader.  The reference hands the .mtl directory to
+ * tinyobj::LoadObj (main.cpp:1613-1620) and never reads the materials again; here each
+ * `newmtl` block becomes one record for rt_scene_set_materials.  Statements that are absent
+ * keep the reference's shader constants (ka .1 .3 .1, kd .2 1 .2, ks .8 .8 .8, ns 100,
+ * ni 1.52).  Returns the number of materials in the file through n_found (which may exceed
+ * max_materials; only the first max_materials are stored). */
+typedef struct rth_material {
+  char name[64];
+  float ka[3], kd[3], ks[3];
+  float ns, ni;
+} rth_material;
+int rth_load_mtl(const char* path, rth_material* out, uint32_t max_materials, uint32_t* n_found);
+
 /* OBJ -> the reference's packed buffers (main.cpp:1603-1729): vertices = n x
  * [px,py,pz,nx,ny,nz]; indices = 3 x uint32 per triangle (polygons fan-triangulated).
  * Buffers are malloc'd; release with rth_free. */

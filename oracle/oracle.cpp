@@ -146,6 +146,7 @@ struct Scene {
   std::vector<Instance> inst;
   std::vector<uint8_t> sky;
   uint32_t sky_w = 0, sky_h = 0;
+  std::vector<rt_material> mat;   // empty: the constants of shader.rgen:51-55 (rt_scene_set_materials)
 };
 
 // inverse of a row-major 3x4 affine matrix: adjugate / determinant in double, rounded
@@ -553,6 +554,34 @@ static inline float pow09(uint32_t i) {  // pow(0.9, float(i)), shader.rgen:128
   return (float)w;
 }
 
+// pow(x, y), 0 <= x <= 1, y > 0, for material exponents other than 100 (rt_b200.h, rt_material):
+// the operation sequence the numeric contract fixes - ln by 2 atanh((m-1)/(m+1)) on the mantissa
+// in [sqrt(1/2), sqrt(2)), exp by Cody-Waite reduction and a degree-13 Taylor polynomial, all in
+// double with explicit fma.
+static inline float det_powf(float xf, float yf) {
+  if (!(xf > 0.0f)) return 0.0f;
+  if (xf >= 1.0f) return 1.0f;
+  const double ln2_hi = 6.93147180369123816490e-01, ln2_lo = 1.90821492927058770002e-10;
+  int e = 0;
+  double m = std::frexp((double)xf, &e);
+  if (m < 0.70710678118654752440) { m = m * 2.0; e -= 1; }
+  const double f = (m - 1.0) / (m + 1.0), f2 = f * f;
+  double p = 1.0 / 23.0;
+  for (int k = 21; k >= 1; k -= 2) p = std::fma(p, f2, 1.0 / (double)k);
+  const double lnx = std::fma((double)e, ln2_hi, std::fma((double)e, ln2_lo, 2.0 * f * p));
+  const double z = (double)yf * lnx;
+  if (z < -745.0) return 0.0f;
+  const double n = std::rint(z * 1.44269504088896338700);
+  double r = std::fma(-n, ln2_hi, z);
+  r = std::fma(-n, ln2_lo, r);
+  static const double inv_fact[14] = {1.0, 1.0, 0.5, 1.0 / 6.0, 1.0 / 24.0, 1.0 / 120.0, 1.0 / 720.0, 1.0 / 5040.0,
+                                      1.0 / 40320.0, 1.0 / 362880.0, 1.0 / 3628800.0, 1.0 / 39916800.0,
+                                      1.0 / 479001600.0, 1.0 / 6227020800.0};
+  double q = inv_fact[13];
+  for (int k = 12; k >= 0; k--) q = std::fma(q, r, inv_fact[k]);
+  return (float)std::ldexp(q, (int)n);
+}
+
 enum { C_PRIMARY = 0, C_SECONDARY, C_SHADOW, C_MISS, C_HIT, C_TRITESTS, C_N = 8 };
 
 struct Frame {
@@ -609,6 +638,20 @@ static V3 render_sample(const Frame& f, uint32_t px, uint32_t py, uint32_t i, rt
       V3 L = normalize(toL);
       if (cnt) cnt[C_SHADOW]++;
       bool shadow = trace_any(s, so, L, 0.001f, dist, f.mode);
+      if (!s.mat.empty()) {   // material of the surface instead of the shader constants
+        const rt_material& mt = s.mat[h.inst];
+        tmp = v3(0.8f * mt.ka[0], 0.8f * mt.ka[1], 0.8f * mt.ka[2]);
+        if (!shadow) {
+          V3 H = normalize(L + neg(dir));
+          float ndl = fmaxf(0.0f, dot(N, L)), ndh = fmaxf(0.0f, dot(N, H));
+          float sp = mt.ns == 100.0f ? pow100(ndh) : det_powf(ndh, mt.ns);
+          float w = pow09(i), I = p.light_intensity;
+          tmp = v3(fmaf(w, (I * mt.kd[0]) * ndl + (I * mt.ks[0]) * sp, tmp.x),
+                   fmaf(w, (I * mt.kd[1]) * ndl + (I * mt.ks[1]) * sp, tmp.y),
+                   fmaf(w, (I * mt.kd[2]) * ndl + (I * mt.ks[2]) * sp, tmp.z));
+        }
+        break;
+      }
       if (!shadow) {
         V3 Vv = neg(dir);
         V3 H = normalize(L + Vv);
@@ -627,7 +670,8 @@ static V3 render_sample(const Frame& f, uint32_t px, uint32_t py, uint32_t i, rt
       float ndoti = dot(dir, N);
       bool outwards = ndoti > 0.0f;
       if (outwards) { N = neg(N); ndoti = -ndoti; }
-      float ratio = outwards ? 1.52f : (1.0f / 1.52f);
+      const float ior = s.mat.empty() ? 1.52f : s.mat[h.inst].ni;
+      float ratio = outwards ? ior : (1.0f / ior);
       float k = 1.0f - (ratio * ratio) * (1.0f - ndoti * ndoti);
       if (k < 0.0f) {
         dir = reflect(dir, N);
@@ -698,6 +742,14 @@ int orc_scene_set_transforms(void* sc, const float* x, uint32_t n) {
   return RT_OK;
 }
 
+int orc_scene_set_materials(void* sc, const rt_material* m, uint32_t n) {
+  Scene* s = (Scene*)sc;
+  s->mat.clear();
+  if (!m) return 0;
+  if (n != s->inst.size()) return 1;
+  s->mat.assign(m, m + n);
+  return 0;
+}
 void orc_scene_destroy(void* sc) { delete (Scene*)sc; }
 
 // Renders the crop [x0,x1) x [y0,y1) of a params->width x params->height frame.
@@ -802,6 +854,7 @@ int orc_trace_f64(void* sc, const float* o3, const float* d3, double tmin, doubl
 }
 
 float orc_det_sin(float x) { return det_sin(x); }
+float orc_det_powf(float x, float y) { return det_powf(x, y); }
 float orc_random(float ux, float uy, float seed) { return random_hash(ux, uy, seed); }
 void orc_sky_sample(void* sc, const float* dir3, float* out3) {
   V3 c = sky_sample(*(Scene*)sc, v3(dir3[0], dir3[1], dir3[2]));

@@ -40,8 +40,10 @@ struct EmuScene {
   uint32_t sky_w = 0, sky_h = 0;
   uint32_t accel = 0;
   std::vector<float4> tlas;
+  std::vector<MaterialDev> mat;
   SceneDev dev() const {
     SceneDev s{};
+    s.mat = mat.empty() ? nullptr : mat.data();
     s.tlas = tlas.empty() ? nullptr : tlas.data();
     s.n_tlas = (uint32_t)(tlas.size() / 4);
     s.blas = blas_dev.data(); s.inst = inst.data(); s.n_inst = (uint32_t)inst.size(); s.accel = accel;
@@ -204,6 +206,15 @@ int emu_scene_create(const rt_scene_desc* d, void** out) {
   return 0;
 }
 void emu_scene_destroy(void* s) { delete (EmuScene*)s; }
+int emu_scene_set_materials(void* s, const rt_material* m, uint32_t n) {
+  EmuScene* es = (EmuScene*)s;
+  es->mat.clear();
+  if (!m) return 0;
+  if (n != es->inst.size()) return 1;
+  es->mat.resize(n);
+  memcpy(es->mat.data(), m, n * sizeof(MaterialDev));
+  return 0;
+}
 uint64_t emu_bvh_nodes(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].nodes; }
 const void* emu_wide_nodes(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].wide.data(); }
 const void* emu_bvh2_nodes(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].bvh2.data(); }
@@ -261,10 +272,11 @@ int emu_render(void* sc, const rt_camera* cam, const rt_frame_params* p, int x0,
               TravCounters tc2{0, 0};
               const bool occ = trace_scene<Stack, true, true>(s, so, L, 0.001f, dist, sh, st, &tc2);
               cnt[6] += tc2.nodes; cnt[7] += tc2.tris;
-              if (!occ) tmp = phong(U, d, N, L, i);
+              if (s.mat) tmp = material_ambient(s.mat[h.inst]);
+              if (!occ) tmp = s.mat ? phong_material(U, s.mat[h.inst], d, N, L, i) : phong(U, d, N, L, i);
               break;
             }
-            scatter(type, P, N, o, d);
+            scatter(type, P, N, o, d, s.mat ? s.mat[h.inst].ni : 1.52f);
           }
           c[0] += tmp.x; c[1] += tmp.y; c[2] += tmp.z; c[3] += 1.0f;
         }

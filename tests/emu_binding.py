@@ -15,6 +15,7 @@ def lib():
         L = C.CDLL(os.path.join(ROOT, "tests", "emu", "libemu.so"))
         L.emu_scene_create.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
         L.emu_scene_destroy.argtypes = [C.c_void_p]
+        L.emu_scene_set_materials.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
         L.emu_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_void_p]
         L.emu_trace.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int, C.c_void_p]
@@ -42,6 +43,14 @@ class EmuScene:
         if self._h and self._h.value:
             lib().emu_scene_destroy(self._h)
             self._h = C.c_void_p()
+
+    def set_materials(self, materials):
+        from vulkan_raytracing_b200 import material_array
+        if materials is None:
+            assert lib().emu_scene_set_materials(self._h, None, 0) == 0
+        else:
+            arr = material_array(materials)
+            assert lib().emu_scene_set_materials(self._h, C.cast(arr, C.c_void_p), len(materials)) == 0
 
     def render(self, camera, params, crop=None):
         from vulkan_raytracing_b200 import HIT_DTYPE

@@ -16,6 +16,7 @@ def lib():
         L.orc_last_error.restype = C.c_char_p
         L.orc_scene_create.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
         L.orc_scene_destroy.argtypes = [C.c_void_p]
+        L.orc_scene_set_materials.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
         L.orc_scene_set_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
         L.orc_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                  C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -24,6 +25,8 @@ def lib():
         L.orc_trace_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
                                     C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]
         L.orc_det_sin.restype = C.c_float
+        L.orc_det_powf.restype = C.c_float
+        L.orc_det_powf.argtypes = [C.c_float, C.c_float]
         L.orc_det_sin.argtypes = [C.c_float]
         L.orc_random.restype = C.c_float
         L.orc_random.argtypes = [C.c_float, C.c_float, C.c_float]
@@ -63,6 +66,14 @@ class OracleScene:
     def set_transforms(self, xforms):
         a = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
         assert lib().orc_scene_set_transforms(self._h, a.ctypes.data, a.shape[0]) == 0
+
+    def set_materials(self, materials):
+        from vulkan_raytracing_b200 import material_array
+        if materials is None:
+            assert lib().orc_scene_set_materials(self._h, None, 0) == 0
+        else:
+            arr = material_array(materials)
+            assert lib().orc_scene_set_materials(self._h, C.cast(arr, C.c_void_p), len(materials)) == 0
 
     def render(self, camera, params, crop=None, brute=False, threads=0, want=("rgba8",)):
         """Returns a dict with any of rgba32f, rgba8, primary, counts over the crop (x0,y0,x1,y1)."""
@@ -104,6 +115,10 @@ class OracleScene:
         out = np.zeros(3, np.float32)
         lib().orc_sky_sample(self._h, d.ctypes.data, out.ctypes.data)
         return out
+
+
+def det_powf(x, y):
+    return lib().orc_det_powf(float(x), float(y))
 
 
 def det_sin(x):

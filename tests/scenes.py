@@ -132,3 +132,13 @@ def c5b_scene(rt, n=16, level=7, sky_size=2048):
             inst.append((0, rt.TYPE_REFRACTIVE if (ix + iz) & 1 else rt.TYPE_DIFFUSE,
                          rt.translation34((ix - 0.5 * (n - 1)) * GRID_PITCH, 0.0, (iz - 0.5 * (n - 1)) * GRID_PITCH)))
     return rt.SceneInputs([(av, ai)], inst, rt.make_procedural_skybox(sky_size))
+
+
+def materials_for(rt, n):
+    """n non-default materials: different exponents (one stays at the reference's 100,
+    one far from it), coloured reflectances, different indices of refraction."""
+    table = [rt.Material.make(ka=(0.3, 0.1, 0.1), kd=(0.9, 0.3, 0.2), ks=(0.5, 0.5, 0.9), ns=17.5, ni=1.33),
+             rt.Material.make(ka=(0.05, 0.05, 0.2), kd=(0.1, 0.2, 0.9), ks=(1.0, 0.8, 0.2), ns=100.0, ni=2.4),
+             rt.Material.make(ka=(0.2, 0.2, 0.0), kd=(0.8, 0.8, 0.1), ks=(0.3, 0.9, 0.3), ns=423.0, ni=1.05),
+             rt.Material.make(ka=(0.0, 0.0, 0.0), kd=(1.0, 1.0, 1.0), ks=(0.0, 0.0, 0.0), ns=1.0, ni=1.52)]
+    return [table[i % len(table)] for i in range(n)]

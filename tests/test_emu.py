@@ -7,10 +7,14 @@ import pytest
 import scenes
 
 
-def compare(rt, ob, emu, inputs, params, accel, cam=None):
+def compare(rt, ob, emu, inputs, params, accel, cam=None, materials=None):
     cam = cam or rt.CameraVectors.default()
-    a = emu.EmuScene(inputs, accel).render(cam, params)
-    b = ob.OracleScene(inputs).render(cam, params, want=("rgba8", "rgba32f", "primary", "counts"))
+    es, osc = emu.EmuScene(inputs, accel), ob.OracleScene(inputs)
+    if materials is not None:
+        es.set_materials(materials)
+        osc.set_materials(materials)
+    a = es.render(cam, params)
+    b = osc.render(cam, params, want=("rgba8", "rgba32f", "primary", "counts"))
     for f in ("instance", "primitive", "t", "u", "v"):
         assert np.array_equal(a["primary"][f], b["primary"][f]), f
     assert np.array_equal(a["rgba32f"], b["rgba32f"])
@@ -23,6 +27,36 @@ def compare(rt, ob, emu, inputs, params, accel, cam=None):
 @pytest.mark.parametrize("accel", [0, 2, 3])
 def test_smoke_scene_bit_exact(rt, ob, emu, accel):
     compare(rt, ob, emu, scenes.smoke_scene(rt), rt.FrameParams.make(96, 72, 6, 3), accel)
+
+
+def test_materials_bit_exact_and_defaults_are_the_reference_constants(rt, ob, emu):
+    """rt_scene_set_materials: emulated kernels == oracle with per-instance Ka/Kd/Ks/Ns/Ni; the default
+    material is bit-identical to no material at all; other materials change the picture."""
+    inputs = scenes.smoke_scene(rt)
+    p = rt.FrameParams.make(96, 72, 6, 3)
+    cam = rt.CameraVectors.default()
+    inputs.instances[0] = (inputs.instances[0][0], rt.TYPE_DIFFUSE, inputs.instances[0][2])   # more lit surface
+    compare(rt, ob, emu, inputs, p, 0, materials=scenes.materials_for(rt, 3))
+    es = emu.EmuScene(inputs, 0)
+    plain = es.render(cam, p)["rgba32f"]
+    es.set_materials([rt.Material.make()] * 3)
+    assert np.array_equal(es.render(cam, p)["rgba32f"], plain)
+    es.set_materials(scenes.materials_for(rt, 3))
+    assert not np.array_equal(es.render(cam, p)["rgba32f"], plain)
+    es.set_materials(None)
+    assert np.array_equal(es.render(cam, p)["rgba32f"], plain)
+
+
+def test_det_powf_against_double_pow(ob):
+    """the fixed-sequence pow of the material exponent: within 1 ulp of the correctly rounded value"""
+    rng = np.random.default_rng(5)
+    x = np.concatenate([rng.uniform(0, 1, 4000), [0.0, 1.0, 1e-30, 0.999999, 0.5]]).astype(np.float32)
+    y = np.concatenate([rng.uniform(0.5, 900, 4000), [17.5, 100.0, 3.0, 423.0, 1.0]]).astype(np.float32)
+    got = np.array([ob.det_powf(a, b) for a, b in zip(x, y)], np.float32)
+    ref = np.power(x.astype(np.float64), y.astype(np.float64))
+    ulp = np.spacing(np.maximum(ref, 1e-38).astype(np.float32)).astype(np.float64)
+    assert np.all(np.abs(got.astype(np.float64) - ref) <= ulp)
+    assert ob.det_powf(0.0, 5.0) == 0.0 and ob.det_powf(1.0, 5.0) == 1.0 and ob.det_powf(0.5, 1.0) == 0.5
 
 
 def test_standin_mesh_refraction_depth8(rt, ob, emu):

@@ -69,6 +69,33 @@ def test_c3_armadillo_standin_depth8(gpu_rt, ob):
     check_frame(gpu_rt, ob, scenes.c3_scene(gpu_rt, level=5, sky_size=256), gpu_rt.FrameParams.make(384, 216, 8, 4))
 
 
+def test_materials_match_the_oracle_and_default_to_the_shader_constants(gpu_rt, ob):
+    """rt_scene_set_materials: per-instance Ka/Kd/Ks/Ns/Ni, bit-exact against the
+    oracle; the default material and NULL both reproduce the reference's constants."""
+    rt = gpu_rt
+    inputs = scenes.c3_scene(rt, level=4, sky_size=128)
+    cam = rt.CameraVectors.default()
+    p = rt.FrameParams.make(320, 180, 8, 4, output_format=rt.FORMAT_RGBA32F)
+    sc = rt.Scene(inputs, device_id=0)
+    plain = sc.render(cam, p)
+    mats = scenes.materials_for(rt, len(inputs.instances))
+    sc.set_materials(mats)
+    got = sc.render(cam, p)
+    osc = ob.OracleScene(inputs)
+    osc.set_materials(mats)
+    ref = osc.render(cam, p, want=("rgba32f",))["rgba32f"]
+    assert np.array_equal(got, ref)
+    assert not np.array_equal(got, plain)
+    sc.set_materials([rt.Material.make()] * len(inputs.instances))
+    assert np.array_equal(sc.render(cam, p), plain)
+    sc.set_materials(mats)
+    sc.set_materials(None)
+    assert np.array_equal(sc.render(cam, p), plain)
+    with pytest.raises(rt.RtError):
+        sc.set_materials(mats[:1] if len(mats) > 1 else mats * 2)
+    sc.close()
+
+
 def test_default_config_depth63_odd_size(gpu_rt, ob):
     """config.h defaults (63 bounces, 4 spp) on a frame that is not a multiple of the tile size."""
     check_frame(gpu_rt, ob, scenes.c1_like_scene(gpu_rt), gpu_rt.FrameParams.make(203, 151, 63, 4))

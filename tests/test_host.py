@@ -165,3 +165,29 @@ def test_headless_host_usage_and_no_device(rt):
         r = subprocess.run([HEADLESS, "--center", "standin:2", "--orbiting", "standin:2", "--skybox", "procedural:8"],
                            capture_output=True, text=True)
         assert r.returncode == 2 and "no CPU fallback" in r.stderr
+
+
+def test_mtl_reader(rt, tmp_path):
+    """rth_load_mtl: every newmtl block becomes a record; absent statements keep the shader constants."""
+    p = tmp_path / "m.mtl"
+    p.write_text("# comment\nnewmtl red\nNs 17.5\nKa 0.3 0.1 0.1\nKd 0.9 0.3 0.2\nKs 0.5 0.5 0.9\nNi 1.33\nd 1.0\nillum 2\n"
+                 "\nnewmtl bare\nKe 0 0 0\n")
+    mats = rt.load_mtl(str(p))
+    assert [n for n, _ in mats] == ["red", "bare"]
+    red, bare = mats[0][1], mats[1][1]
+    assert np.allclose(list(red.ka), [0.3, 0.1, 0.1]) and np.allclose(list(red.kd), [0.9, 0.3, 0.2])
+    assert np.allclose(list(red.ks), [0.5, 0.5, 0.9]) and red.ns == np.float32(17.5) and red.ni == np.float32(1.33)
+    d = rt.Material.make()
+    assert bytes(bare) == bytes(d)
+    with pytest.raises(RuntimeError):
+        rt.load_mtl(str(tmp_path / "missing.mtl"))
+
+
+def test_reference_mtl_files_parse(rt):
+    """the .mtl files the reference ships (ignored by its shaders): Blender exports with Ns 225 / Ni 1.45"""
+    root = "/root/reference/resources"
+    if not os.path.isdir(root):
+        pytest.skip("reference tree not present")
+    mats = rt.load_mtl(os.path.join(root, "teapot.mtl"))
+    assert len(mats) == 1 and mats[0][0] == "teapot" and mats[0][1].ns == 225.0 and mats[0][1].ni == np.float32(1.45)
+    assert len(rt.load_mtl(os.path.join(root, "cube_scene.mtl"))) == 8

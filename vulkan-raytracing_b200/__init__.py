@@ -104,6 +104,26 @@ class FrameParams(C.Structure):
         return q
 
 
+class Material(C.Structure):
+    """rt_material: Ka / Kd / Ks / Ns / Ni of one instance; the defaults are the constants of shader.rgen:51-55, :125."""
+    _fields_ = [("ka", C.c_float * 3), ("kd", C.c_float * 3), ("ks", C.c_float * 3), ("ns", C.c_float), ("ni", C.c_float)]
+
+    @staticmethod
+    def make(ka=(0.1, 0.3, 0.1), kd=(0.2, 1.0, 0.2), ks=(0.8, 0.8, 0.8), ns=100.0, ni=1.52) -> "Material":
+        m = Material()
+        m.ka[:], m.kd[:], m.ks[:] = [float(x) for x in ka], [float(x) for x in kd], [float(x) for x in ks]
+        m.ns, m.ni = float(ns), float(ni)
+        return m
+
+
+def material_array(materials):
+    """list of Material -> contiguous ctypes array (what rt_scene_set_materials takes)."""
+    arr = (Material * len(materials))()
+    for i, m in enumerate(materials):
+        C.memmove(C.byref(arr, i * C.sizeof(Material)), C.byref(m), C.sizeof(Material))
+    return arr
+
+
 class IpcHandle(C.Structure):
     _fields_ = [("opaque", C.c_uint8 * 64)]
 
@@ -165,6 +185,7 @@ def host_lib():
         L.rth_make_standin_armadillo.argtypes = [C.c_uint32, C.c_uint32, C.c_float, fpp, u32p, upp, u32p]
         L.rth_make_grid.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
                                     C.c_float, fpp, u32p, upp, u32p]
+        L.rth_load_mtl.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
         L.rth_load_skybox_dir.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_uint8)), u32p, u32p]
         L.rth_make_procedural_skybox.argtypes = [C.c_uint32, C.c_void_p]
         L.rth_camera_create.restype = C.c_void_p
@@ -222,6 +243,24 @@ def make_grid(V: np.ndarray, I: np.ndarray, nx: int, nz: int, pitch: float):
     _hcheck(L.rth_make_grid(V.ctypes.data, V.shape[0], I.ctypes.data, I.shape[0], nx, nz, pitch, C.byref(v),
                             C.byref(nv), C.byref(i), C.byref(nt)))
     return _take_mesh(v, nv, i, nt)
+
+
+class HostMaterial(C.Structure):
+    _fields_ = [("name", C.c_char * 64), ("ka", C.c_float * 3), ("kd", C.c_float * 3), ("ks", C.c_float * 3),
+                ("ns", C.c_float), ("ni", C.c_float)]
+
+
+def load_mtl(path: str):
+    """Wavefront .mtl -> [(name, Material), ...] in file order (rth_load_mtl)."""
+    L = host_lib()
+    n = C.c_uint32(0)
+    buf = (HostMaterial * 256)()
+    _hcheck(L.rth_load_mtl(path.encode(), buf, 256, C.byref(n)))
+    out = []
+    for i in range(min(n.value, 256)):
+        h = buf[i]
+        out.append((h.name.decode(), Material.make(tuple(h.ka), tuple(h.kd), tuple(h.ks), h.ns, h.ni)))
+    return out
 
 
 def load_skybox_dir(path: str) -> np.ndarray:
@@ -345,6 +384,7 @@ def rt_lib():
         L.rt_scene_build.argtypes = [C.POINTER(SceneDesc), C.POINTER(C.c_void_p)]
         L.rt_scene_set_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
         L.rt_scene_destroy.argtypes = [C.c_void_p]
+        L.rt_scene_set_materials.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
         L.rt_scene_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.rt_set_counting.argtypes = [C.c_void_p, C.c_int]
         L.rt_render_frame.argtypes = [C.c_void_p, C.POINTER(CameraVectors), C.POINTER(FrameParams), C.c_void_p]
@@ -403,6 +443,14 @@ class Scene:
     def set_transforms(self, xforms):
         a = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
         _check(rt_lib().rt_scene_set_transforms(self._h, a.ctypes.data, a.shape[0]))
+
+    def set_materials(self, materials):
+        """One Material per instance, or None to return to the reference's shader constants."""
+        if materials is None:
+            _check(rt_lib().rt_scene_set_materials(self._h, None, 0))
+        else:
+            arr = material_array(materials)
+            _check(rt_lib().rt_scene_set_materials(self._h, C.cast(arr, C.c_void_p), len(materials)))
 
     def set_stream(self, cuda_stream: int):
         _check(rt_lib().rt_scene_set_stream(self._h, C.c_void_p(cuda_stream)))

@@ -21,6 +21,7 @@ struct Scene {
   std::vector<InstDev> inst;
   BlasDev* d_blas = nullptr;
   InstDev* d_inst = nullptr;
+  MaterialDev* d_mat = nullptr;  // nullptr: the reference's shader constants
   std::vector<float4> tlas;      // host copy of the top-level tree (rt_tlas.hpp)
   float4* d_tlas = nullptr;
   size_t d_tlas_cap = 0;
@@ -36,6 +37,7 @@ struct Scene {
     SceneDev s{};
     s.blas = d_blas;
     s.inst = d_inst;
+    s.mat = d_mat;
     s.n_inst = (uint32_t)inst.size();
     s.accel = accel;
     s.sky = d_sky;
@@ -121,7 +123,7 @@ static void destroy_scene(Scene* s) {
   if (!s) return;
   cudaSetDevice(s->device);
   for (auto& b : s->blas) free_blas(b);
-  cudaFree(s->d_blas); cudaFree(s->d_inst); cudaFree(s->d_tlas); cudaFree(s->d_sky); cudaFree(s->d_out);
+  cudaFree(s->d_blas); cudaFree(s->d_inst); cudaFree(s->d_mat); cudaFree(s->d_tlas); cudaFree(s->d_sky); cudaFree(s->d_out);
   pipeline_destroy(s->pipe);
   delete s;
 }
@@ -273,6 +275,26 @@ int rt_scene_set_transforms(void* scene, const float* xforms12, uint32_t n) {
   RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
   for (uint32_t i = 0; i < n; i++) set_instance(*s, i, xforms12 + 12 * (size_t)i);
   return upload_instances(*s);
+}
+
+int rt_scene_set_materials(void* scene, const rt_material* materials, uint32_t n) {
+  Scene* s = (Scene*)scene;
+  if (!s) return fail(RT_ERR_INVALID_ARGUMENT, "null scene");
+  RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
+  if (!materials) {  // back to shader.rgen:51-55
+    RT_CUDA_TRY(cudaStreamSynchronize(s->stream), g_err);
+    cudaFree(s->d_mat);
+    s->d_mat = nullptr;
+    return RT_OK;
+  }
+  if (n != s->inst.size()) return fail(RT_ERR_INVALID_ARGUMENT, "one material per instance");
+  static_assert(sizeof(MaterialDev) == sizeof(rt_material), "material layout");
+  for (uint32_t i = 0; i < n; i++)
+    if (!(materials[i].ns > 0.0f) || !(materials[i].ni > 0.0f)) return fail(RT_ERR_INVALID_ARGUMENT, "material needs ns > 0 and ni > 0");
+  if (!s->d_mat) RT_CUDA_TRY(cudaMalloc(&s->d_mat, n * sizeof(MaterialDev)), g_err);
+  RT_CUDA_TRY(cudaMemcpyAsync(s->d_mat, materials, n * sizeof(MaterialDev), cudaMemcpyHostToDevice, s->stream), g_err);
+  RT_CUDA_TRY(cudaStreamSynchronize(s->stream), g_err);
+  return RT_OK;
 }
 
 int rt_scene_destroy(void* scene) {

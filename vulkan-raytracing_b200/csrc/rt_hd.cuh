@@ -187,6 +187,35 @@ RT_HD float pow100(float x) {
   float p2 = x * x, p4 = p2 * p2, p8 = p4 * p4, p16 = p8 * p8, p32 = p16 * p16, p64 = p32 * p32;
   return (p64 * p32) * p4;
 }
+// pow(x, y) for 0 <= x <= 1, y > 0 with a fixed operation sequence (materials with Ns != 100):
+// double precision, ln(x) = e ln2 + 2 atanh((m-1)/(m+1)) with m in [sqrt(1/2), sqrt(2)), then
+// exp by Cody-Waite reduction and a degree-13 Taylor polynomial; every step is an IEEE
+// operation, so host and device agree bit for bit.
+RT_HD float det_powf(float xf, float yf) {
+  if (!(xf > 0.0f)) return 0.0f;
+  if (xf >= 1.0f) return 1.0f;
+  const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
+  int e = 0;
+  double m = frexp((double)xf, &e);               // m in [0.5, 1)
+  if (m < 0.70710678118654752440) { m = m * 2.0; e -= 1; }
+  const double f = (m - 1.0) / (m + 1.0), f2 = f * f;
+  double p = 1.0 / 23.0;
+  p = fma(p, f2, 1.0 / 21.0); p = fma(p, f2, 1.0 / 19.0); p = fma(p, f2, 1.0 / 17.0); p = fma(p, f2, 1.0 / 15.0);
+  p = fma(p, f2, 1.0 / 13.0); p = fma(p, f2, 1.0 / 11.0); p = fma(p, f2, 1.0 / 9.0); p = fma(p, f2, 1.0 / 7.0);
+  p = fma(p, f2, 1.0 / 5.0); p = fma(p, f2, 1.0 / 3.0); p = fma(p, f2, 1.0);
+  const double lnx = fma((double)e, LN2_HI, fma((double)e, LN2_LO, 2.0 * f * p));
+  const double z = (double)yf * lnx;               // <= 0
+  if (z < -745.0) return 0.0f;
+  const double n = rint(z * 1.44269504088896338700);
+  double r = fma(-n, LN2_HI, z);
+  r = fma(-n, LN2_LO, r);
+  double q = 1.0 / 6227020800.0;
+  q = fma(q, r, 1.0 / 479001600.0); q = fma(q, r, 1.0 / 39916800.0); q = fma(q, r, 1.0 / 3628800.0);
+  q = fma(q, r, 1.0 / 362880.0); q = fma(q, r, 1.0 / 40320.0); q = fma(q, r, 1.0 / 5040.0); q = fma(q, r, 1.0 / 720.0);
+  q = fma(q, r, 1.0 / 120.0); q = fma(q, r, 1.0 / 24.0); q = fma(q, r, 1.0 / 6.0); q = fma(q, r, 0.5);
+  q = fma(q, r, 1.0); q = fma(q, r, 1.0);
+  return (float)ldexp(q, (int)n);
+}
 // pow(0.9, float(i)) of shader.rgen:128: repeated double multiply, rounded once
 RT_HD float pow09(uint32_t i) {
   double w = 1.0;

@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(256) k_shade_miss(SceneDev scene, const uint32
 __global__ void __launch_bounds__(256)
     k_shade_diffuse(SceneDev scene, uint32_t* __restrict__ cnt, const uint32_t* __restrict__ qDiff,
                     const float4* __restrict__ rayO, const float4* __restrict__ rayD, const uint4* __restrict__ hits,
-                    float4* __restrict__ shadowQ) {
+                    float4* __restrict__ shadowQ, float4* __restrict__ sample) {
   const uint32_t n = cnt[C_NDIFF];
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -277,26 +277,37 @@ __global__ void __launch_bounds__(256)
     const uint32_t i = (uint32_t)base + lane_id();
     bool emit = false;
     f3 P = mk3(0, 0, 0), N = mk3(0, 0, 0), d = mk3(0, 0, 0);
-    uint32_t s = 0;
+    uint32_t s = 0, inst = 0;
     if (i < n) {
       const uint32_t idx = qDiff[i];
       const uint4 h = hits[idx];
       const float4 rd = rayD[idx];
       s = __float_as_uint(rayO[idx].w);
       d = mk3(rd.x, rd.y, rd.z);
+      inst = h.x;
       rchit(scene, h.x, h.y, __uint_as_float(h.z), __uint_as_float(h.w), P, N);
       emit = !(dot3(d, N) >= 0.0f);  // shader.rgen:104-105: back face keeps the ambient colour
     }
     const uint32_t dst = warp_append(emit, &cnt[C_NSHADOW]);
     if (emit) {
+      if (scene.mat) {  // rt_scene_set_materials: the surface's own ambient term, lit or not
+        const f3 amb = material_ambient(scene.mat[inst]);
+        sample[s] = make_float4(amb.x, amb.y, amb.z, 1.0f);
+      }
       shadowQ[3 * (size_t)dst + 0] = make_float4(P.x, P.y, P.z, __uint_as_float(s));
-      shadowQ[3 * (size_t)dst + 1] = make_float4(N.x, N.y, N.z, 0.0f);
+      shadowQ[3 * (size_t)dst + 1] = make_float4(N.x, N.y, N.z, __uint_as_float(inst));
       shadowQ[3 * (size_t)dst + 2] = make_float4(d.x, d.y, d.z, 0.0f);
     }
   }
 }
 
 // ---- shadow rays + Phong ----------------------------------------------------------------------
+// colour of an unshadowed diffuse hit; inst_bits = the instance id k_shade_diffuse left in the queue
+__device__ __forceinline__ f3 lit_color(const SceneDev& scene, const FrameUniforms& U, float inst_bits, f3 d, f3 N, f3 L,
+                                        uint32_t i) {
+  return scene.mat ? phong_material(U, scene.mat[__float_as_uint(inst_bits)], d, N, L, i) : phong(U, d, N, L, i);
+}
+
 struct ShadowSource {
   const FrameUniforms& U;
   const float4* shadowQ;
@@ -309,6 +320,7 @@ struct ShadowSource {
 };
 
 struct ShadowSink {
+  const SceneDev& scene;
   const FrameUniforms& U;
   const float4* shadowQ;
   float4* sample;
@@ -320,7 +332,7 @@ struct ShadowSink {
       float dist;
       shadow_ray(U, P, N, so, L, dist);
       const uint32_t s = __float_as_uint(q0.w);
-      const f3 c = phong(U, mk3(q2.x, q2.y, q2.z), N, L, s % U.spp);
+      const f3 c = lit_color(scene, U, q1.w, mk3(q2.x, q2.y, q2.z), N, L, s % U.spp);
       sample[s] = make_float4(c.x, c.y, c.z, 1.0f);
     }
   }
@@ -341,7 +353,7 @@ __global__ void RT_TRACE_BOUNDS
 #ifdef RT_WITH_PERSIST
   if (ACCEL == ACCEL_WIDE && refill_thresh > 0) {  // RT_REFILL=0: run-to-completion loop
     ShadowSource src{U, shadowQ};
-    ShadowSink sink{U, shadowQ, sample};
+    ShadowSink sink{scene, U, shadowQ, sample};
     trace_wide_persistent<true, COUNT>(scene, n, &cnt[C_WSHADOW], st, src, sink, tc, refill_thresh, tri_thresh);
   } else
 #endif
@@ -361,7 +373,7 @@ __global__ void RT_TRACE_BOUNDS
       HitRec h;
       const bool occluded = trace_scene_t<ACCEL, true, COUNT>(scene, so, L, 0.001f, dist, h, st, &tc);
       if (!occluded) {
-        const f3 c = phong(U, d, N, L, s % U.spp);
+        const f3 c = lit_color(scene, U, q1.w, d, N, L, s % U.spp);
         sample[s] = make_float4(c.x, c.y, c.z, 1.0f);
       }
     }
@@ -461,7 +473,7 @@ __global__ void RT_TRACE_BOUNDS
   st.loc = stack_loc;
   TravCounters tc{0ull, 0ull};
   const WaveShadowSource src{U, shadowQ};
-  const ShadowSink sink{U, shadowQ, sample};
+  const ShadowSink sink{scene, U, shadowQ, sample};
   wave_trace<true, COUNT>(scene, cnt[C_NSHADOW], &cnt[C_WSHADOW], st, src, sink, tc, refill_min, tri_min);
   if (COUNT) {
     atomicAdd(&stats64[2], tc.nodes);
@@ -516,7 +528,7 @@ __global__ void __launch_bounds__(256)
       d = mk3(rd.x, rd.y, rd.z);
       f3 P, N;
       rchit(scene, h.x, h.y, __uint_as_float(h.z), __uint_as_float(h.w), P, N);
-      scatter(scene.inst[h.x].type, P, N, o, d);
+      scatter(scene.inst[h.x].type, P, N, o, d, scene.mat ? scene.mat[h.x].ni : 1.52f);
     }
     const uint32_t dst = warp_append(active, &cntNext[C_NRAY]);
     if (active) {
@@ -791,7 +803,8 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 1], st), err);
 #undef CALL_TRACE
     k_shade_miss<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qMiss, p->rayO[cur], p->rayD[cur], p->sample);
-    k_shade_diffuse<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qDiff, p->rayO[cur], p->rayD[cur], p->hits, p->shadowQ);
+    k_shade_diffuse<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qDiff, p->rayO[cur], p->rayD[cur], p->hits, p->shadowQ,
+                                                    p->sample);
 #define CALL_SHADOW(A, C)                                                                                 \
   {                                                                                                       \
     static int blocks = 0;                                                                                \

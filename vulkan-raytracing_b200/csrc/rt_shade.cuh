@@ -126,7 +126,7 @@ RT_HD f3 sky_sample(const SceneDev& s, f3 r) {
 
 // shader.rgen:132-165: mirror / refraction with total internal reflection.  Any other
 // type value falls through the reference's if/else chain and leaves the ray unchanged.
-RT_HD void scatter(uint32_t type, f3 P, f3 N, f3& o, f3& d) {
+RT_HD void scatter(uint32_t type, f3 P, f3 N, f3& o, f3& d, float ior = 1.52f) {
   if (type == 1u) {
     o = madd3(0.01f, N, P);
     d = reflect3(d, N);
@@ -134,7 +134,7 @@ RT_HD void scatter(uint32_t type, f3 P, f3 N, f3& o, f3& d) {
     float ndoti = dot3(d, N);
     const bool outwards = ndoti > 0.0f;
     if (outwards) { N = neg3(N); ndoti = -ndoti; }
-    const float ratio = outwards ? 1.52f : (1.0f / 1.52f);
+    const float ratio = outwards ? ior : (1.0f / ior);   // index_of_refraction, shader.rgen:51 (or the material's Ni)
     const float k = 1.0f - (ratio * ratio) * (1.0f - ndoti * ndoti);
     if (k < 0.0f) {
       d = reflect3(d, N);
@@ -163,6 +163,18 @@ RT_HD f3 phong(const FrameUniforms& U, f3 dir, f3 N, f3 L, uint32_t i) {
   const f3 amb = ambient_color();
   return mk3(fmaf(w, (I * 0.2f) * ndl + (I * 0.8f) * sp, amb.x), fmaf(w, (I * 1.0f) * ndl + (I * 0.8f) * sp, amb.y),
              fmaf(w, (I * 0.2f) * ndl + (I * 0.8f) * sp, amb.z));
+}
+
+// the same with a material (rt_scene_set_materials): ambient, diffuse and specular reflectance and
+// the exponent come from the instance; ns == 100 takes the reference's multiply chain
+RT_HD f3 material_ambient(const MaterialDev& m) { return mk3(0.8f * m.ka[0], 0.8f * m.ka[1], 0.8f * m.ka[2]); }
+RT_HD f3 phong_material(const FrameUniforms& U, const MaterialDev& m, f3 dir, f3 N, f3 L, uint32_t i) {
+  const f3 H = normalize3(add3(L, neg3(dir)));
+  const float ndl = fmaxf(0.0f, dot3(N, L)), ndh = fmaxf(0.0f, dot3(N, H));
+  const float sp = m.ns == 100.0f ? pow100(ndh) : det_powf(ndh, m.ns), w = pow09(i), I = U.intensity;
+  const f3 amb = material_ambient(m);
+  return mk3(fmaf(w, (I * m.kd[0]) * ndl + (I * m.ks[0]) * sp, amb.x), fmaf(w, (I * m.kd[1]) * ndl + (I * m.ks[1]) * sp, amb.y),
+             fmaf(w, (I * m.kd[2]) * ndl + (I * m.ks[2]) * sp, amb.z));
 }
 
 RT_HD uint32_t to_unorm8(float c) {

@@ -35,9 +35,16 @@ struct InstDev {
   uint32_t type;
 };
 
+// per-instance material (rt_material); SceneDev::mat == nullptr means the constants of shader.rgen:51-55
+struct MaterialDev {
+  float ka[3], kd[3], ks[3];
+  float ns, ni;
+};
+
 struct SceneDev {
   const BlasDev* blas;
   const InstDev* inst;
+  const MaterialDev* mat;
   uint32_t n_inst;
   uint32_t accel;
   const uint8_t* sky;  // 6 x h x w x RGBA8

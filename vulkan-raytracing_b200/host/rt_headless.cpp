@@ -50,6 +50,8 @@ void usage() {
       "  --out PREFIX          write PREFIX_%04d.ppm for every frame\n"
       "  --device N            CUDA ordinal (default 0)\n"
       "  --accel N             RT_ACCEL_* flavour (default 0)\n"
+      "  --materials           shade each mesh with the first material of the .mtl next to its .obj\n"
+      "                        (the reference parses these files and then uses shader constants)\n"
       "  --fps                 TEST_FPS: print per-frame times and the FPS summary");
 }
 
@@ -81,6 +83,7 @@ int main(int argc, char** argv) {
   int device = 0;
   float dt = 1.0f / 60.0f;
   std::string out_prefix;
+  bool use_materials = false;
   for (int a = 1; a < argc; a++) {
     const std::string k = argv[a];
     auto val = [&]() -> const char* {
@@ -103,6 +106,7 @@ int main(int argc, char** argv) {
     else if (k == "--device") device = std::atoi(val());
     else if (k == "--accel") accel = (uint32_t)std::atoi(val());
     else if (k == "--fps") cfg.test_fps = true;
+    else if (k == "--materials") use_materials = true;
     else { std::fprintf(stderr, "unknown option %s\n", k.c_str()); usage(); return 1; }
   }
   if (rt_device_count() < 1) {
@@ -153,6 +157,31 @@ int main(int argc, char** argv) {
     return 1;
   }
   if (sky_malloced) rth_free(sky);
+  if (use_materials) {   // foo.obj -> foo.mtl, first newmtl block; a mesh without one keeps the shader constants
+    rt_material mats[2];
+    const std::string* objs[2] = {&cfg.center_mesh_obj_path, &cfg.orbiting_mesh_obj_path};
+    for (int i = 0; i < 2; i++) {
+      const float ka[3] = {0.1f, 0.3f, 0.1f}, kd[3] = {0.2f, 1.0f, 0.2f}, ks[3] = {0.8f, 0.8f, 0.8f};
+      std::memcpy(mats[i].ka, ka, sizeof ka); std::memcpy(mats[i].kd, kd, sizeof kd); std::memcpy(mats[i].ks, ks, sizeof ks);
+      mats[i].ns = 100.0f; mats[i].ni = 1.52f;
+      std::string mtl = (*objs[i])[0] == '/' ? *objs[i] : cfg.resource_root + "/" + *objs[i];
+      const size_t dot = mtl.rfind(".obj");
+      if (dot == std::string::npos) continue;
+      mtl.replace(dot, 4, ".mtl");
+      rth_material hm;
+      uint32_t found = 0;
+      if (rth_load_mtl(mtl.c_str(), &hm, 1, &found) == 0 && found > 0) {
+        std::memcpy(mats[i].ka, hm.ka, sizeof hm.ka); std::memcpy(mats[i].kd, hm.kd, sizeof hm.kd);
+        std::memcpy(mats[i].ks, hm.ks, sizeof hm.ks);
+        mats[i].ns = hm.ns; mats[i].ni = hm.ni;
+        std::printf("material %d: %s from %s (Ns %g, Ni %g)\n", i, hm.name, mtl.c_str(), hm.ns, hm.ni);
+      }
+    }
+    if (rt_scene_set_materials(scene, mats, 2) != RT_OK) {
+      std::fprintf(stderr, "rt_scene_set_materials: %s\n", rt_last_error());
+      return 1;
+    }
+  }
   rt_stats st{};
   rt_get_stats(scene, &st);
   std::printf("scene: %u + %u triangles, BVH %llu nodes / %.1f MB, built in %.2f ms\n", center.nt, orbiting.nt,

@@ -234,6 +234,46 @@ int rth_load_obj(const char* path, float** vertices, uint32_t* n_vertices, uint3
   return 0;
 }
 
+int rth_load_mtl(const char* path, rth_material* out, uint32_t max_materials, uint32_t* n_found) {
+  if (!path || !n_found || (max_materials && !out)) { g_err = "rth_load_mtl: null argument"; return 1; }
+  FILE* f = std::fopen(path, "rb");
+  if (!f) { g_err = std::string("cannot open ") + path; return 1; }
+  uint32_t n = 0;
+  rth_material cur;
+  bool open_block = false;
+  auto flush = [&]() {
+    if (!open_block) return;
+    if (n < max_materials) out[n] = cur;
+    n++;
+  };
+  char line[1024];
+  while (std::fgets(line, sizeof line, f)) {
+    char key[32] = "", name[64] = "";
+    float v[3] = {0.f, 0.f, 0.f};
+    if (std::sscanf(line, " %31s", key) != 1 || key[0] == '#') continue;
+    if (!std::strcmp(key, "newmtl")) {
+      flush();
+      std::memset(&cur, 0, sizeof cur);
+      const float ka[3] = {0.1f, 0.3f, 0.1f}, kd[3] = {0.2f, 1.0f, 0.2f}, ks[3] = {0.8f, 0.8f, 0.8f};  // shader.rgen:52-55
+      std::memcpy(cur.ka, ka, sizeof ka); std::memcpy(cur.kd, kd, sizeof kd); std::memcpy(cur.ks, ks, sizeof ks);
+      cur.ns = 100.0f; cur.ni = 1.52f;                                                                 // :125, :51
+      if (std::sscanf(line, " %*s %63s", name) == 1) std::snprintf(cur.name, sizeof cur.name, "%s", name);
+      open_block = true;
+    } else if (open_block) {
+      const int got = std::sscanf(line, " %*s %f %f %f", &v[0], &v[1], &v[2]);
+      if (got == 3 && !std::strcmp(key, "Ka")) std::memcpy(cur.ka, v, sizeof v);
+      else if (got == 3 && !std::strcmp(key, "Kd")) std::memcpy(cur.kd, v, sizeof v);
+      else if (got == 3 && !std::strcmp(key, "Ks")) std::memcpy(cur.ks, v, sizeof v);
+      else if (got >= 1 && !std::strcmp(key, "Ns") && v[0] > 0.0f) cur.ns = v[0];
+      else if (got >= 1 && !std::strcmp(key, "Ni") && v[0] > 0.0f) cur.ni = v[0];
+    }
+  }
+  flush();
+  std::fclose(f);
+  *n_found = n;
+  return 0;
+}
+
 int rth_make_standin_armadillo(uint32_t level, uint32_t seed, float radius, float** vertices,
                                uint32_t* n_vertices, uint32_t** indices, uint32_t* n_triangles) {
   if (level > 10) return fail(-1, "level too large");

@@ -62,6 +62,9 @@ enum {
 #define RT_FLAG_ACCEL_MASK 0xFu
 /* Skip the SAH treelet refinement of the Karras tree (faster build, slower rays). */
 #define RT_FLAG_NO_REFINE 0x10u
+/* Ignore the normal slots of every mesh and fill them on the device with area-weighted
+ * vertex normals (rt_generate_normals) before the build: for meshes whose file has no vn. */
+#define RT_FLAG_GENERATE_NORMALS 0x20u
 
 /* One triangle mesh = one bottom-level acceleration structure.
  * Replaces createBLASGeometry/createBLAS/buildBLAS (main.cpp:305-536) and the
@@ -180,6 +183,17 @@ uint32_t rt_abi_version(void);
 const char* rt_last_error(void);
 /* Number of CUDA devices visible; 0 when there is none (never an error). */
 int rt_device_count(void);
+
+/* --- assets ----------------------------------------------------------------- */
+/* Area-weighted vertex normals for a mesh that has none (the
+ * reference can only take `vn` records from the file, main.cpp:1647-1683).
+ * vertices = n_vertices x [px,py,pz,nx,ny,nz] on the HOST: positions are read, the
+ * normal slots are overwritten.  Computed on the GPU with the arithmetic and the
+ * summation order of the host loader (rth_generate_normals in rt_host.h), so both
+ * give the same bits.  device_ms (may be NULL) receives the CUDA-event time of the
+ * kernels, copies excluded. */
+int rt_generate_normals(int device_id, float* vertices, uint32_t n_vertices, const uint32_t* indices,
+                        uint32_t n_triangles, double* device_ms);
 
 /* --- scene ------------------------------------------------------------------ */
 /* main.cpp:1603-1835 + 2061-2412.  Builds every BLAS on the GPU. */

@@ -24,6 +24,11 @@ enum {
 const char* rth_last_error(void);
 void rth_free(void* p);
 
+/* Area-weighted vertex normals of a packed mesh (n x [px,py,pz,nx,ny,nz], normal slots
+ * overwritten): what rth_load_obj applies to files without `vn` (RTH_PACK_GENERATED), exposed
+ * so that rt_generate_normals (the same on the GPU, rt_b200.h) can be checked against it. */
+int rth_generate_normals(float* vertices, uint32_t n_vertices, const uint32_t* indices, uint32_t n_triangles);
+
 /* Wavefront .mtl reader.  The reference hands the .mtl directory to
  * tinyobj::LoadObj (main.cpp:1613-1620) and never reads the materials again; here each
  * `newmtl` block becomes one record for rt_scene_set_materials.  Statements that are absent

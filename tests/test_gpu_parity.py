@@ -255,6 +255,40 @@ def test_error_paths(gpu_rt):
     sc.close()
 
 
+def test_device_normals_equal_the_host_loader(gpu_rt):
+    """rt_generate_normals == rth_generate_normals bit for bit: full-size stand-in mesh,
+    an unused vertex, a degenerate triangle, a vertex shared by very many triangles, an empty mesh."""
+    rt = gpu_rt
+    v, i = rt.make_standin_armadillo(7)
+    rng = np.random.default_rng(3)
+    v = v.copy()
+    v[:, :3] += rng.normal(0, 1e-3, (v.shape[0], 3)).astype(np.float32)
+    v[:, 3:] = 0
+    v = np.vstack([v, np.array([[9, 9, 9, 0, 0, 0]], np.float32)])
+    fan = np.stack([np.zeros(5000, np.uint32), rng.integers(1, 4000, 5000).astype(np.uint32),
+                    rng.integers(1, 4000, 5000).astype(np.uint32)], 1)
+    i = np.vstack([i, np.array([[0, 0, 1]], np.uint32), fan])
+    dev, ms = rt.generate_normals(v, i)
+    host = rt.generate_normals_host(v, i)
+    assert np.array_equal(dev, host)
+    assert ms > 0
+    # RT_FLAG_GENERATE_NORMALS: a scene built from the normal-less mesh renders like one built from host normals
+    sky = rt.make_procedural_skybox(32)
+    small_v, small_i = rt.make_standin_armadillo(3)
+    bare = small_v.copy()
+    bare[:, 3:] = 0
+    cam, p = rt.CameraVectors.default(), rt.FrameParams.make(160, 120, 3, 2, output_format=rt.FORMAT_RGBA32F)
+    inst = [(0, rt.TYPE_DIFFUSE, rt.IDENTITY34)]
+    a = rt.Scene(rt.SceneInputs([(bare, small_i)], inst, sky), device_id=0, accel=rt.FLAG_GENERATE_NORMALS)
+    b = rt.Scene(rt.SceneInputs([(rt.generate_normals_host(bare, small_i), small_i)], inst, sky), device_id=0)
+    assert np.array_equal(a.render(cam, p), b.render(cam, p))
+    a.close(); b.close()
+    e, _ = rt.generate_normals(np.zeros((3, 6), np.float32), np.zeros((0, 3), np.uint32))
+    assert np.array_equal(e[:, 3:], [[0, 1, 0]] * 3)
+    with pytest.raises(rt.RtError):
+        rt.generate_normals(np.zeros((3, 6), np.float32), np.array([[0, 1, 3]], np.uint32))
+
+
 def test_sort_pairs_matches_numpy(gpu_rt):
     rng = np.random.default_rng(3)
     for n in (1, 31, 4096, 4097, 300001, 3000001):   # the last one: more tiles than resident blocks

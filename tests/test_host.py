@@ -191,3 +191,22 @@ def test_reference_mtl_files_parse(rt):
     mats = rt.load_mtl(os.path.join(root, "teapot.mtl"))
     assert len(mats) == 1 and mats[0][0] == "teapot" and mats[0][1].ns == 225.0 and mats[0][1].ni == np.float32(1.45)
     assert len(rt.load_mtl(os.path.join(root, "cube_scene.mtl"))) == 8
+
+
+def test_host_normals_equal_a_numpy_restatement(rt):
+    """rth_generate_normals: area-weighted, summed per vertex in triangle order in double (np.add.at keeps
+    that order), normalised in double, rounded once; unused vertices get (0,1,0)."""
+    v, i = rt.make_standin_armadillo(3)
+    v = np.vstack([v, np.array([[9, 9, 9, 0, 0, 0]], np.float32)])       # a vertex no triangle uses
+    i = np.vstack([i, np.array([[0, 0, 1]], np.uint32)])                  # a degenerate triangle
+    got = rt.generate_normals_host(v, i)
+    pos = v[:, :3].astype(np.float64)
+    a, b, c = pos[i[:, 0]], pos[i[:, 1]], pos[i[:, 2]]
+    n = np.cross(b - a, c - a)
+    acc = np.zeros_like(pos)
+    np.add.at(acc, i.reshape(-1), np.repeat(n, 3, axis=0))
+    l = np.sqrt(acc[:, 0] * acc[:, 0] + acc[:, 1] * acc[:, 1] + acc[:, 2] * acc[:, 2])
+    ref = np.where(l[:, None] == 0, np.array([0.0, 1.0, 0.0]), acc / np.where(l == 0, 1, l)[:, None]).astype(np.float32)
+    assert np.array_equal(got[:, 3:], ref)
+    assert np.array_equal(got[:, :3], v[:, :3])
+    assert np.array_equal(got[-1, 3:], [0, 1, 0])

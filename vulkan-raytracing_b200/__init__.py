@@ -33,6 +33,7 @@ LOCATION_HOST, LOCATION_DEVICE = 0, 1
 SHARD_COMPACT, SHARD_IN_FRAME = 0, 1
 ACCEL_DEFAULT, ACCEL_BVH2, ACCEL_BRUTE, ACCEL_WIDE8 = 0, 1, 2, 3
 FLAG_NO_REFINE = 0x10
+FLAG_GENERATE_NORMALS = 0x20
 MISS = 0xFFFFFFFF
 
 
@@ -185,6 +186,7 @@ def host_lib():
         L.rth_make_standin_armadillo.argtypes = [C.c_uint32, C.c_uint32, C.c_float, fpp, u32p, upp, u32p]
         L.rth_make_grid.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
                                     C.c_float, fpp, u32p, upp, u32p]
+        L.rth_generate_normals.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]
         L.rth_load_mtl.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
         L.rth_load_skybox_dir.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_uint8)), u32p, u32p]
         L.rth_make_procedural_skybox.argtypes = [C.c_uint32, C.c_void_p]
@@ -384,6 +386,7 @@ def rt_lib():
         L.rt_scene_build.argtypes = [C.POINTER(SceneDesc), C.POINTER(C.c_void_p)]
         L.rt_scene_set_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
         L.rt_scene_destroy.argtypes = [C.c_void_p]
+        L.rt_generate_normals.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.POINTER(C.c_double)]
         L.rt_scene_set_materials.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
         L.rt_scene_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.rt_set_counting.argtypes = [C.c_void_p, C.c_int]
@@ -532,6 +535,24 @@ class PeerFrame:
             L = rt_lib()
             _check((L.rt_peer_frame_destroy if self.owner else L.rt_peer_frame_close)(self.device_id, C.c_void_p(self.ptr)))
             self.ptr = 0
+
+
+def generate_normals(vertices: np.ndarray, indices: np.ndarray, device_id: int = 0):
+    """Area-weighted vertex normals on the GPU (rt_generate_normals): returns (vertices with the normal
+    slots filled, device milliseconds)."""
+    v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 6).copy()
+    i = np.ascontiguousarray(indices, np.uint32).reshape(-1, 3)
+    ms = C.c_double(0.0)
+    _check(rt_lib().rt_generate_normals(device_id, v.ctypes.data, v.shape[0], i.ctypes.data, i.shape[0], C.byref(ms)))
+    return v, ms.value
+
+
+def generate_normals_host(vertices: np.ndarray, indices: np.ndarray) -> np.ndarray:
+    """The host loader's version of the same (rth_generate_normals)."""
+    v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 6).copy()
+    i = np.ascontiguousarray(indices, np.uint32).reshape(-1, 3)
+    _hcheck(host_lib().rth_generate_normals(v.ctypes.data, v.shape[0], i.ctypes.data, i.shape[0]))
+    return v
 
 
 def measure_fp32_tflops(device_id: int = 0) -> float:

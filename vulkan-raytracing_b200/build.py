@@ -41,7 +41,7 @@ def run(cmd, **kw):
 
 def build_cuda(force=False, verbose=False):
     csrc = os.path.join(HERE, "csrc")
-    srcs = [os.path.join(csrc, f) for f in ("rt_api.cu", "rt_build.cu", "rt_sort.cu", "rt_render.cu")]
+    srcs = [os.path.join(csrc, f) for f in ("rt_api.cu", "rt_build.cu", "rt_sort.cu", "rt_normals.cu", "rt_render.cu")]
     deps = srcs + [os.path.join(csrc, f) for f in os.listdir(csrc)] + [os.path.join(ROOT, "include", "rt_b200.h")]
     out = os.path.join(HERE, "librt_b200.so")
     if not force and not _newer(out, deps):

@@ -222,6 +222,10 @@ int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
       RT_CUDA_TRY(cudaMalloc(&b.d_idx, (size_t)m.n_triangles * 12), g_err);
       RT_CUDA_TRY(cudaMemcpy(b.d_idx, m.indices, (size_t)m.n_triangles * 12, cudaMemcpyHostToDevice), g_err);
     }
+    if ((d->flags & RT_FLAG_GENERATE_NORMALS) && m.n_vertices) {  // meshes without vn: normals made where the data already is
+      int rc = generate_normals(b.d_verts, m.n_vertices, b.d_idx, m.n_triangles, s->stream, nullptr, g_err);
+      if (rc != RT_OK) return rc;
+    }
   }
   RT_CUDA_TRY(cudaEventRecord(e0, s->stream), g_err);
   for (uint32_t i = 0; i < d->n_meshes; i++) {
@@ -361,6 +365,30 @@ int rt_render_frame(void* scene, const rt_camera* cam, const rt_frame_params* p,
   Scene* s = (Scene*)scene;
   if (!s || !rgba_out) return fail(RT_ERR_INVALID_ARGUMENT, "null scene or output");
   return render_common(s, cam, p, rgba_out, nullptr);
+}
+
+int rt_generate_normals(int device_id, float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt, double* device_ms) {
+  if (!vertices || (nt && !indices)) return fail(RT_ERR_INVALID_ARGUMENT, "null mesh");
+  if (rt_device_count() < 1) return fail(RT_ERR_NO_DEVICE, "no CUDA device");
+  for (uint64_t i = 0; i < 3ull * nt; i++)
+    if (indices[i] >= nv) return fail(RT_ERR_INVALID_ARGUMENT, "vertex index out of range");
+  RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
+  float* dv = nullptr;
+  uint32_t* di = nullptr;
+  const size_t vb = (size_t)nv * 6 * sizeof(float), ib = (size_t)nt * 3 * sizeof(uint32_t);
+  cudaError_t e = cudaMalloc(&dv, vb ? vb : 4);
+  if (e == cudaSuccess) e = cudaMalloc(&di, ib ? ib : 4);
+  if (e == cudaSuccess) e = cudaMemcpy(dv, vertices, vb, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess && ib) e = cudaMemcpy(di, indices, ib, cudaMemcpyHostToDevice);
+  int rc = RT_OK;
+  float ms = 0.f;
+  if (e == cudaSuccess) rc = generate_normals(dv, nv, di, nt, nullptr, &ms, g_err);
+  if (e == cudaSuccess && rc == RT_OK) e = cudaMemcpy(vertices, dv, vb, cudaMemcpyDeviceToHost);
+  cudaFree(dv);
+  cudaFree(di);
+  if (e != cudaSuccess) return fail(e == cudaErrorMemoryAllocation ? RT_ERR_OUT_OF_MEMORY : RT_ERR_CUDA, cudaGetErrorString(e));
+  if (rc == RT_OK && device_ms) *device_ms = ms;
+  return rc;
 }
 
 // ---- frame buffers other processes can store into (CUDA IPC over NVLink peer access) ----------

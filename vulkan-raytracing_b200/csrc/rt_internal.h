@@ -45,6 +45,10 @@ int sort_pairs_u32(uint32_t* keys, uint32_t* keys_alt, uint32_t* vals, uint32_t*
 size_t sort_hist_words(uint64_t n);
 int sort_launches(int key_bits);
 
+// Area-weighted vertex normals of a packed mesh on the device (rt_normals.cu).
+int generate_normals(float* d_verts, uint32_t nv, const uint32_t* d_idx, uint32_t nt, cudaStream_t st, float* ms_out,
+                     std::string& err);
+
 // Per-scene wavefront buffers and the frame pipeline.
 struct FramePipeline;
 FramePipeline* pipeline_create();

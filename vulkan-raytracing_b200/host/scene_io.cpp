@@ -234,6 +234,18 @@ int rth_load_obj(const char* path, float** vertices, uint32_t* n_vertices, uint3
   return 0;
 }
 
+int rth_generate_normals(float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt) {
+  if (!vertices || (nt && !indices)) { g_err = "rth_generate_normals: null mesh"; return 1; }
+  for (uint64_t i = 0; i < 3ull * nt; i++)
+    if (indices[i] >= nv) { g_err = "rth_generate_normals: vertex index out of range"; return 1; }
+  std::vector<float> pos(3 * (size_t)nv), nrm;
+  for (size_t v = 0; v < nv; v++) std::memcpy(&pos[3 * v], &vertices[6 * v], 3 * sizeof(float));
+  std::vector<uint32_t> idx(indices, indices + 3 * (size_t)nt);
+  area_weighted_normals(pos, idx, nrm);
+  for (size_t v = 0; v < nv; v++) std::memcpy(&vertices[6 * v + 3], &nrm[3 * v], 3 * sizeof(float));
+  return 0;
+}
+
 int rth_load_mtl(const char* path, rth_material* out, uint32_t max_materials, uint32_t* n_found) {
   if (!path || !n_found || (max_materials && !out)) { g_err = "rth_load_mtl: null argument"; return 1; }
   FILE* f = std::fopen(path, "rb");

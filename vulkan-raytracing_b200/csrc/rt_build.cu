@@ -149,12 +149,26 @@ static int grid_for(uint64_t n, int block) {
   return (int)std::max<uint64_t>(1, std::min(want, cap));
 }
 
+// Scratch of one build: a single arena reserved before the first kernel (cudaMalloc of several GB
+// takes 0.1-1 s and used to sit between the kernels, inside the timed region), handed out in
+// 256-byte aligned pieces; a request the arena cannot serve falls back to its own allocation.
 struct TempAlloc {
   std::vector<void*> ptrs;
+  char* arena = nullptr;
+  size_t cap = 0, used = 0;
   ~TempAlloc() { for (void* p : ptrs) cudaFree(p); }
-  template <class T> cudaError_t get(T** p, size_t count) {
+  cudaError_t reserve(size_t bytes) {
     void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+    cudaError_t e = cudaMalloc(&q, bytes);
+    if (e == cudaSuccess) { ptrs.push_back(q); arena = (char*)q; cap = bytes; used = 0; }
+    else cudaGetLastError();   // too large for one piece: the pieces are tried one by one
+    return cudaSuccess;
+  }
+  template <class T> cudaError_t get(T** p, size_t count) {
+    const size_t bytes = (std::max<size_t>(count, 1) * sizeof(T) + 255) & ~(size_t)255;
+    if (used + bytes <= cap) { *p = (T*)(arena + used); used += bytes; return cudaSuccess; }
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, bytes);
     if (e == cudaSuccess) { ptrs.push_back(q); *p = (T*)q; }
     return e;
   }
@@ -165,7 +179,9 @@ void free_blas(BlasHost& b) {
   b = BlasHost{};
 }
 
-int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refine, cudaStream_t stream, std::string& err) {
+int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refine, cudaStream_t stream, float* kernel_ms,
+               std::string& err) {
+  if (kernel_ms) *kernel_ms = 0.0f;
   b.dev.verts = b.d_verts;
   b.dev.idx = b.d_idx;
   b.dev.ntri = ntri;
@@ -177,6 +193,15 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
   if (ntri == 0) return RT_OK;
   const size_t N = ntri;
   TempAlloc tmp;
+  {  // bytes per triangle of every array requested below (+ the 8-wide staging), plus slack for alignment
+    size_t per_tri = 32 + 16;
+    if (accel != ACCEL_BRUTE) per_tri += 16 + 8 + 8 + 12 + 4 + 64 + 4 + (refine ? 8 + 8 : 0) + (accel == ACCEL_WIDE ? 80 + 4 : 0);
+    tmp.reserve(N * per_tri + sort_hist_words(N) * sizeof(uint32_t) + (1u << 20));
+  }
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  RT_CUDA_TRY(cudaEventCreate(&ev0), err);
+  RT_CUDA_TRY(cudaEventCreate(&ev1), err);
+  struct EvGuard { cudaEvent_t &a, &b; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } ev_guard{ev0, ev1};
   BuildArrays a{};
   a.verts = b.d_verts;
   a.idx = b.d_idx;
@@ -188,6 +213,17 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
   RT_CUDA_TRY(tmp.get(&a.tri_hi, N), err);
   RT_CUDA_TRY(tmp.get(&a.bounds, 16), err);
   RT_CUDA_TRY(cudaMalloc(&b.d_tris, N * 48), err);
+  if (accel == ACCEL_BVH2) RT_CUDA_TRY(cudaMalloc(&b.d_nodes, std::max<size_t>(N - 1, 1) * 64), err);
+  RT_CUDA_TRY(cudaEventRecord(ev0, stream), err);
+  static const bool dbg = getenv("RT_DEBUG_BUILD") != nullptr;   // phase times on stderr
+  std::vector<std::pair<const char*, cudaEvent_t>> marks;
+  auto mark = [&](const char* name) {
+    if (!dbg) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, stream);
+    marks.push_back({name, e});
+  };
   k_init_bounds<<<1, 32, 0, stream>>>(a.bounds);
   k_tri_boxes<<<grid_for(N, 256), 256, 0, stream>>>(a);
   if (accel != ACCEL_BRUTE) {
@@ -205,10 +241,14 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
     RT_CUDA_TRY(tmp.get(&a.flags, N), err);
     RT_CUDA_TRY(cudaMemsetAsync(a.flags, 0, N * sizeof(uint32_t), stream), err);
     k_morton<<<grid_for(N, 256), 256, 0, stream>>>(a);
+    mark("boxes+morton");
     int rc = sort_pairs(a.keys, keys_alt, a.vals, vals_alt, N, 63, hist, stream, err);
     if (rc != RT_OK) return rc;
+    mark("sort");
     if (ntri > 1) k_karras<<<grid_for(N, 256), 256, 0, stream>>>(a);
+    mark("karras");
     k_refit<<<grid_for(N, 256), 256, 0, stream>>>(a);
+    mark("refit");
     static const int treelet_passes = getenv("RT_TREELET_PASSES") ? atoi(getenv("RT_TREELET_PASSES")) : 1;
     if (ntri > 2 && refine && treelet_passes > 0) {
       RT_CUDA_TRY(tmp.get(&a.cost, 2 * N), err);
@@ -221,6 +261,7 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
         RT_CUDA_TRY(cudaMemsetAsync(a.flags, 0, N * sizeof(uint32_t), stream), err);
         RT_CUDA_TRY(cudaMemsetAsync(qcount, 0, 2 * sizeof(uint32_t), stream), err);
         k_treelet_leaves<<<grid_for(N, 256), 256, 0, stream>>>(a, queue[0], qcount);
+        mark("treelet leaves");
         int cur = 0;
         for (int round = 0; round < 4096; round++) {
           uint32_t count = 0;
@@ -229,8 +270,10 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
           if (count == 0) break;
           RT_CUDA_TRY(cudaMemsetAsync(qcount + (cur ^ 1), 0, sizeof(uint32_t), stream), err);
           k_treelet_round<<<grid_for(count, 128), 128, 0, stream>>>(a, queue[cur], count, queue[cur ^ 1], qcount + (cur ^ 1));
+          if (dbg && round < 6) mark("treelet round");
           cur ^= 1;
         }
+        mark("treelet rounds (rest)");
       }
     }
   }
@@ -259,7 +302,6 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
     RT_CUDA_TRY(cudaMemcpyAsync(b.d_nodes, wide_tmp, (size_t)end * 80, cudaMemcpyDeviceToDevice, stream), err);
     b.bytes = (uint64_t)end * 80 + N * 48;
   } else if (accel == ACCEL_BVH2) {
-    RT_CUDA_TRY(cudaMalloc(&b.d_nodes, std::max<size_t>(N - 1, 1) * 64), err);
     k_emit_bvh2<<<grid_for(N, 256), 256, 0, stream>>>(a, (float4*)b.d_nodes, (float4*)b.d_tris);
     b.node_count = N - 1;
     b.bytes = (uint64_t)(N - 1) * 64 + N * 48;
@@ -268,9 +310,24 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
     b.bytes = N * 48;
   }
   uint32_t hb[12];
+  RT_CUDA_TRY(cudaEventRecord(ev1, stream), err);
   RT_CUDA_TRY(cudaMemcpyAsync(hb, a.bounds, sizeof hb, cudaMemcpyDeviceToHost, stream), err);
   RT_CUDA_TRY(cudaStreamSynchronize(stream), err);
   RT_CUDA_TRY(cudaGetLastError(), err);
+  if (kernel_ms) cudaEventElapsedTime(kernel_ms, ev0, ev1);
+  if (dbg) {
+    cudaEvent_t prev = ev0;
+    for (auto& m : marks) {
+      float t = 0.f;
+      cudaEventElapsedTime(&t, prev, m.second);
+      fprintf(stderr, "  build %-22s %9.3f ms\n", m.first, t);
+      prev = m.second;
+    }
+    float t = 0.f;
+    cudaEventElapsedTime(&t, prev, ev1);
+    fprintf(stderr, "  build %-22s %9.3f ms  (N = %zu)\n", "emit", t, N);
+    for (auto& m : marks) cudaEventDestroy(m.second);
+  }
   float amax = 0.0f;
   for (int k = 0; k < 6; k++) amax = std::max(amax, std::fabs(ordered_to_float(hb[k])));
   const float pad = amax * 4e-6f + 1e-30f;

@@ -31,7 +31,8 @@ struct BlasHost {
 };
 
 // Builds the acceleration structure of one mesh already resident on the device.
-int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refine, cudaStream_t stream, std::string& err);
+int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refine, cudaStream_t stream, float* kernel_ms,
+               std::string& err);
 void free_blas(BlasHost& b);
 
 // One-sweep LSD radix sort of (key,value) pairs (rt_sort.cu), 8 bits per pass over `key_bits`

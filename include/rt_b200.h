@@ -158,7 +158,8 @@ typedef struct rt_stats {
   double build_ms;            /* all BLAS builds + TLAS, CUDA events */
   double frame_ms;            /* last frame, CUDA events, device side only */
   double trace_ms;            /* closest-hit traversal kernels of the last frame */
-  double shadow_ms;           /* shadow traversal kernels */
+  double shadow_ms;           /* shadow traversal kernels: the part not overlapped by a closest-hit launch
+                                 (they run on a second stream); trace_ms + shadow_ms = time a traversal kernel ran */
   double shade_ms;            /* raygen + shading + resolve kernels */
   uint64_t rays_primary;      /* closest-hit traces at bounce 0 */
   uint64_t rays_secondary;    /* closest-hit traces at bounce >= 1 */

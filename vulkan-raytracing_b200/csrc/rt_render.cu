@@ -658,6 +658,8 @@ struct FramePipeline {
   uint32_t* h_alive = nullptr;   // pinned: rays entering bounce j, copied back without stalling the stream
   size_t alive_cap = 0;
   std::vector<cudaEvent_t> aev;  // aev[j]: h_alive[j] has landed
+  cudaStream_t aux = nullptr;    // shadow rays of bounce j run here, beside bounce j+1's closest-hit rays
+  std::vector<cudaEvent_t> sev;  // sev[2j]: shadow queue of bounce j is complete, sev[2j+1]: its shadow rays are done
 };
 
 FramePipeline* pipeline_create() { return new FramePipeline(); }
@@ -678,6 +680,8 @@ void pipeline_destroy(FramePipeline* p) {
   for (auto& e : p->ev) if (e) cudaEventDestroy(e);
   for (auto& e : p->kev) cudaEventDestroy(e);
   for (auto& e : p->aev) cudaEventDestroy(e);
+  for (auto& e : p->sev) cudaEventDestroy(e);
+  if (p->aux) cudaStreamDestroy(p->aux);
   if (p->h_alive) cudaFreeHost(p->h_alive);
   delete p;
 }
@@ -723,6 +727,12 @@ static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std:
     p->h_alive = nullptr;
     p->alive_cap = bounces + 2;
     RT_CUDA_TRY(cudaHostAlloc(&p->h_alive, p->alive_cap * sizeof(uint32_t), cudaHostAllocDefault), err);
+  }
+  if (!p->aux) RT_CUDA_TRY(cudaStreamCreateWithFlags(&p->aux, cudaStreamNonBlocking), err);
+  while (p->sev.size() < 2 * (bounces + 1)) {
+    cudaEvent_t e;
+    RT_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), err);
+    p->sev.push_back(e);
   }
   while (p->aev.size() < bounces + 2) {
     cudaEvent_t e;
@@ -770,6 +780,13 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   static const bool wave_on = getenv("RT_WAVE") ? atoi(getenv("RT_WAVE")) != 0 : false;
   static const int wave_refill = getenv("RT_WAVE_REFILL") ? atoi(getenv("RT_WAVE_REFILL")) : 12;
   static const int wave_tri = getenv("RT_WAVE_TRI") ? atoi(getenv("RT_WAVE_TRI")) : 6;
+  // Shadow rays of bounce j only feed the radiance slots of paths that have ended, so they need
+  // not finish before bounce j+1 starts: they go to a second stream and their last batches (and
+  // the launches that carry a handful of rays) overlap the next closest-hit launch.  The shadow
+  // queue is single-buffered: k_shade_diffuse of bounce j+1 waits for them.  RT_SHADOW_STREAM=0
+  // puts everything back on one stream.
+  static const bool shadow_async = getenv("RT_SHADOW_STREAM") ? atoi(getenv("RT_SHADOW_STREAM")) != 0 : true;
+  cudaStream_t sst = shadow_async ? p->aux : st;
   const uint32_t* perm = nullptr;
   uint64_t launches = 0;
   RT_CUDA_TRY(cudaEventRecord(p->ev[0], st), err);
@@ -803,23 +820,29 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 1], st), err);
 #undef CALL_TRACE
     k_shade_miss<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qMiss, p->rayO[cur], p->rayD[cur], p->sample);
+    if (shadow_async && j > 0) RT_CUDA_TRY(cudaStreamWaitEvent(st, p->sev[2 * (j - 1) + 1], 0), err);
     k_shade_diffuse<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qDiff, p->rayO[cur], p->rayD[cur], p->hits, p->shadowQ,
                                                     p->sample);
+    if (shadow_async) {
+      RT_CUDA_TRY(cudaEventRecord(p->sev[2 * j], st), err);
+      RT_CUDA_TRY(cudaStreamWaitEvent(sst, p->sev[2 * j], 0), err);
+    }
 #define CALL_SHADOW(A, C)                                                                                 \
   {                                                                                                       \
     static int blocks = 0;                                                                                \
     if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
-    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, refill_t, tri_t); \
+    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, refill_t, tri_t); \
   }
-    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 2], st), err);
+    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 2], sst), err);
     if (wave) {
       static int wb[2] = {0, 0};
       if (!wb[0]) { wb[0] = persistent_blocks(k_shadow_wave<false>, TRACE_THREADS); wb[1] = persistent_blocks(k_shadow_wave<true>, TRACE_THREADS); }
-      if (counting) k_shadow_wave<true><<<wb[1], TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
-      else k_shadow_wave<false><<<wb[0], TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
+      if (counting) k_shadow_wave<true><<<wb[1], TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
+      else k_shadow_wave<false><<<wb[0], TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
     } else
     RT_DISPATCH_ACCEL(accel, counting, CALL_SHADOW);
-    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 3], st), err);
+    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 3], sst), err);
+    if (shadow_async) RT_CUDA_TRY(cudaEventRecord(p->sev[2 * j + 1], sst), err);
 #undef CALL_SHADOW
     launches += 4;
     last_bounce = j;
@@ -849,6 +872,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
       if (dead) break;
     }
   }
+  if (shadow_async) RT_CUDA_TRY(cudaStreamWaitEvent(st, p->sev[2 * last_bounce + 1], 0), err);
   if (rq.d_out) {
     k_resolve<<<stride_blocks(npix, 256), 256, 0, st>>>(U, (uint32_t)npix, p->sample, rq.d_out, rq.output_format);
     launches++;
@@ -866,12 +890,28 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]);
     stats->frame_ms = ms;
     double tr = 0.0, sh = 0.0;
+    // trace_ms = the closest-hit launches; shadow_ms = the part of the shadow launches that is not
+    // hidden behind one of them (they run on a second stream), so trace_ms + shadow_ms is the time
+    // during which a traversal kernel was running: the union of all launch intervals
+    std::vector<std::pair<float, float>> iv;
     for (uint32_t j = 0; j <= last_bounce; j++) {
-      float a = 0.f, b = 0.f;
-      cudaEventElapsedTime(&a, p->kev[4 * j + 0], p->kev[4 * j + 1]);
-      cudaEventElapsedTime(&b, p->kev[4 * j + 2], p->kev[4 * j + 3]);
-      tr += a; sh += b;
+      float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+      cudaEventElapsedTime(&a0, p->ev[0], p->kev[4 * j + 0]);
+      cudaEventElapsedTime(&a1, p->ev[0], p->kev[4 * j + 1]);
+      cudaEventElapsedTime(&b0, p->ev[0], p->kev[4 * j + 2]);
+      cudaEventElapsedTime(&b1, p->ev[0], p->kev[4 * j + 3]);
+      tr += a1 - a0;
+      iv.push_back({a0, a1});
+      iv.push_back({b0, b1});
     }
+    std::sort(iv.begin(), iv.end());
+    double uni = 0.0;
+    float cur_end = -1.0f;
+    for (auto& x : iv) {
+      const float s0 = std::max(x.first, cur_end);
+      if (x.second > s0) { uni += x.second - s0; cur_end = x.second; }
+    }
+    sh = std::max(0.0, uni - tr);
     stats->trace_ms = tr;
     static const bool dbg = getenv("RT_DEBUG_BOUNCES") != nullptr;
     if (dbg) {
@@ -885,7 +925,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
       }
     }
     stats->shadow_ms = sh;
-    stats->shade_ms = ms - tr - sh;
+    stats->shade_ms = std::max(0.0, (double)ms - tr - sh);   // (trace and shadow intervals may overlap)
     // primary traces = rays traversed + rays the top level answered in k_raygen
     stats->rays_primary = (uint64_t)p->h_cnt[C_NRAY] + p->h_cnt[C_NCULL];
     stats->rays_secondary = stats->rays_shadow = stats->n_hit = 0;

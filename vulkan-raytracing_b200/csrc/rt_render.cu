@@ -83,18 +83,20 @@ __device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t* counter) {
 // A primary ray that reaches no instance's padded world box is answered here, at the top level
 // of the scene (what the TLAS does for traceRayEXT): the miss shader's sky lookup runs at once and
 // the ray never enters the queue.  Only rays with something to traverse are written to HBM.
-__global__ void __launch_bounds__(256) k_raygen(SceneDev scene, FrameUniforms U, uint32_t nslots, float4* __restrict__ rayO,
-                                                float4* __restrict__ rayD, float4* __restrict__ sample,
-                                                uint32_t* __restrict__ cnt, rt_hit* __restrict__ primary) {
+// Works on the slots [slot_base, slot_base + nslots) of the frame (one sub-frame).
+__global__ void __launch_bounds__(256) k_raygen(SceneDev scene, FrameUniforms U, uint32_t slot_base, uint32_t nslots,
+                                                float4* __restrict__ rayO, float4* __restrict__ rayD,
+                                                float4* __restrict__ sample, uint32_t* __restrict__ cnt,
+                                                rt_hit* __restrict__ primary) {
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const f3 amb = ambient_color();
   uint32_t culled = 0;
   for (uint64_t base = (uint64_t)w * 32; base < nslots; base += (uint64_t)warps * 32) {
-    const uint32_t s = (uint32_t)base + lane_id();
+    const uint32_t s = slot_base + (uint32_t)base + lane_id();
     bool valid = false, reach = false;
     f3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
-    if (s < nslots) {
+    if ((uint32_t)base + lane_id() < nslots) {
       uint32_t x, y;
       valid = slot_to_pixel(U, s / U.spp, x, y);
       if (valid) {
@@ -639,6 +641,7 @@ __global__ void __launch_bounds__(TRACE_THREADS)
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
+static const int RT_MAX_SUB = 4;
 struct FramePipeline {
   size_t cap = 0;  // ray slots the buffers hold
   float4 *rayO[2] = {nullptr, nullptr}, *rayD[2] = {nullptr, nullptr};
@@ -654,12 +657,19 @@ struct FramePipeline {
   unsigned long long* stats64 = nullptr;
   std::vector<uint32_t> h_cnt;
   cudaEvent_t ev[2] = {nullptr, nullptr};
-  std::vector<cudaEvent_t> kev;  // per bounce: trace begin/end, shadow begin/end
-  uint32_t* h_alive = nullptr;   // pinned: rays entering bounce j, copied back without stalling the stream
-  size_t alive_cap = 0;
-  std::vector<cudaEvent_t> aev;  // aev[j]: h_alive[j] has landed
-  cudaStream_t aux = nullptr;    // shadow rays of bounce j run here, beside bounce j+1's closest-hit rays
-  std::vector<cudaEvent_t> sev;  // sev[2j]: shadow queue of bounce j is complete, sev[2j+1]: its shadow rays are done
+  // A frame is rendered as up to two independent sub-frames (halves of the tile list), each with its
+  // own slice of the buffers, counters, streams and events: see pipeline_render.
+  struct Sub {
+    cudaStream_t own = nullptr;    // main stream of sub-frame 1 (sub-frame 0 runs on the caller's stream)
+    cudaStream_t aux = nullptr;    // shadow rays of bounce j run here, beside bounce j+1's closest-hit rays
+    std::vector<cudaEvent_t> kev;  // per bounce: trace begin/end, shadow begin/end
+    std::vector<cudaEvent_t> sev;  // sev[2j]: shadow queue of bounce j complete, sev[2j+1]: its shadow rays done
+    std::vector<cudaEvent_t> aev;  // aev[j]: h_alive[j] has landed
+    uint32_t* h_alive = nullptr;   // pinned: rays entering bounce j, copied back without stalling the stream
+    size_t alive_cap = 0;
+    cudaEvent_t done = nullptr;
+  } sub[RT_MAX_SUB];
+  cudaEvent_t start = nullptr;
 };
 
 FramePipeline* pipeline_create() { return new FramePipeline(); }
@@ -678,11 +688,16 @@ void pipeline_destroy(FramePipeline* p) {
   pipeline_free_buffers(p);
   cudaFree(p->cnt); cudaFree(p->stats64);
   for (auto& e : p->ev) if (e) cudaEventDestroy(e);
-  for (auto& e : p->kev) cudaEventDestroy(e);
-  for (auto& e : p->aev) cudaEventDestroy(e);
-  for (auto& e : p->sev) cudaEventDestroy(e);
-  if (p->aux) cudaStreamDestroy(p->aux);
-  if (p->h_alive) cudaFreeHost(p->h_alive);
+  for (auto& sb : p->sub) {
+    for (auto& e : sb.kev) cudaEventDestroy(e);
+    for (auto& e : sb.aev) cudaEventDestroy(e);
+    for (auto& e : sb.sev) cudaEventDestroy(e);
+    if (sb.done) cudaEventDestroy(sb.done);
+    if (sb.aux) cudaStreamDestroy(sb.aux);
+    if (sb.own) cudaStreamDestroy(sb.own);
+    if (sb.h_alive) cudaFreeHost(sb.h_alive);
+  }
+  if (p->start) cudaEventDestroy(p->start);
   delete p;
 }
 
@@ -706,38 +721,45 @@ static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std:
     RT_CUDA_TRY(cudaMalloc(&p->sortH, sort_hist_words(slots) * sizeof(uint32_t)), err);
     p->cap = slots;
   }
-  if (bounces + 2 > p->cnt_blocks) {
+  if (bounces + 2 > p->cnt_blocks) {   // one set of per-bounce counter blocks per sub-frame
     cudaFree(p->cnt);
     p->cnt = nullptr;
     p->cnt_blocks = bounces + 2;
-    RT_CUDA_TRY(cudaMalloc(&p->cnt, p->cnt_blocks * C_STRIDE * sizeof(uint32_t)), err);
+    RT_CUDA_TRY(cudaMalloc(&p->cnt, RT_MAX_SUB * p->cnt_blocks * C_STRIDE * sizeof(uint32_t)), err);
   }
   if (!p->stats64) RT_CUDA_TRY(cudaMalloc(&p->stats64, 8 * sizeof(unsigned long long)), err);
   if (!p->ev[0]) {
     RT_CUDA_TRY(cudaEventCreate(&p->ev[0]), err);
     RT_CUDA_TRY(cudaEventCreate(&p->ev[1]), err);
+    RT_CUDA_TRY(cudaEventCreateWithFlags(&p->start, cudaEventDisableTiming), err);
   }
-  while (p->kev.size() < 4 * (bounces + 1)) {
-    cudaEvent_t e;
-    RT_CUDA_TRY(cudaEventCreate(&e), err);
-    p->kev.push_back(e);
-  }
-  if (bounces + 2 > p->alive_cap) {
-    if (p->h_alive) cudaFreeHost(p->h_alive);
-    p->h_alive = nullptr;
-    p->alive_cap = bounces + 2;
-    RT_CUDA_TRY(cudaHostAlloc(&p->h_alive, p->alive_cap * sizeof(uint32_t), cudaHostAllocDefault), err);
-  }
-  if (!p->aux) RT_CUDA_TRY(cudaStreamCreateWithFlags(&p->aux, cudaStreamNonBlocking), err);
-  while (p->sev.size() < 2 * (bounces + 1)) {
-    cudaEvent_t e;
-    RT_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), err);
-    p->sev.push_back(e);
-  }
-  while (p->aev.size() < bounces + 2) {
-    cudaEvent_t e;
-    RT_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), err);
-    p->aev.push_back(e);
+  for (auto& sb : p->sub) {
+    if (!sb.aux) {
+      RT_CUDA_TRY(cudaStreamCreateWithFlags(&sb.aux, cudaStreamNonBlocking), err);
+      RT_CUDA_TRY(cudaStreamCreateWithFlags(&sb.own, cudaStreamNonBlocking), err);
+      RT_CUDA_TRY(cudaEventCreateWithFlags(&sb.done, cudaEventDisableTiming), err);
+    }
+    while (sb.kev.size() < 4 * (bounces + 1)) {
+      cudaEvent_t e;
+      RT_CUDA_TRY(cudaEventCreate(&e), err);
+      sb.kev.push_back(e);
+    }
+    if (bounces + 2 > sb.alive_cap) {
+      if (sb.h_alive) cudaFreeHost(sb.h_alive);
+      sb.h_alive = nullptr;
+      sb.alive_cap = bounces + 2;
+      RT_CUDA_TRY(cudaHostAlloc(&sb.h_alive, sb.alive_cap * sizeof(uint32_t), cudaHostAllocDefault), err);
+    }
+    while (sb.sev.size() < 2 * (bounces + 1)) {
+      cudaEvent_t e;
+      RT_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), err);
+      sb.sev.push_back(e);
+    }
+    while (sb.aev.size() < bounces + 2) {
+      cudaEvent_t e;
+      RT_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), err);
+      sb.aev.push_back(e);
+    }
   }
   return RT_OK;
 }
@@ -761,6 +783,30 @@ static int stride_blocks(uint64_t n, int threads) {
     else { if (counting) { CALL(ACCEL_BRUTE, true); } else { CALL(ACCEL_BRUTE, false); } }                            \
   } while (0)
 
+// One frame.  The tile list is cut into RT_SUBFRAMES consecutive parts that are rendered as independent
+// sub-frames, each on its own stream (plus one stream each for their shadow rays).  A persistent traversal launch ends
+// with a few warps still working on their last 32-ray batch while the rest of the GPU idles
+// (≈ 0.1 ms per launch, 18 launches per frame); with several sub-frames in flight the blocks of another
+// part's launch move in as soon as blocks retire, so those tails are filled.  Each sample
+// owns its radiance slot, so the split does not change a single bit of the image.
+// RT_SUBFRAMES=1 renders the frame in one piece.
+namespace {
+struct SubCtx {
+  FramePipeline::Sub* sb;
+  cudaStream_t st, sst;
+  uint32_t slot_base, nslots;
+  float4 *rayO[2], *rayD[2];
+  uint4* hits;
+  uint32_t *qMiss, *qDiff, *qSpec;
+  float4* shadowQ;
+  uint32_t* cnt;
+  int cur = 0;
+  bool dead = false;
+  uint32_t last_bounce = 0;
+  const uint32_t* perm = nullptr;
+};
+}  // namespace
+
 int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, rt_stats* stats, std::string& err) {
   const FrameUniforms& U = rq.U;
   const uint64_t npix = (uint64_t)U.n_local_tiles * U.tile_w * U.tile_h;
@@ -771,7 +817,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   if (rc != RT_OK) return rc;
   const uint32_t accel = rq.scene.accel;
   const bool counting = rq.counting;
-  // tuning knobs of the persistent traversal (defaults from the r02 sweep, profiles/)
+  // tuning knobs of the persistent traversal (defaults from the sweeps under profiles/)
   static const int refill_t = getenv("RT_REFILL") ? atoi(getenv("RT_REFILL")) : 0;
   static const int tri_t = getenv("RT_TRITHRESH") ? atoi(getenv("RT_TRITHRESH")) : 8;
   static const int sort_from = getenv("RT_SORT_FROM") ? atoi(getenv("RT_SORT_FROM")) : 1000;
@@ -786,93 +832,141 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   // queue is single-buffered: k_shade_diffuse of bounce j+1 waits for them.  RT_SHADOW_STREAM=0
   // puts everything back on one stream.
   static const bool shadow_async = getenv("RT_SHADOW_STREAM") ? atoi(getenv("RT_SHADOW_STREAM")) != 0 : true;
-  cudaStream_t sst = shadow_async ? p->aux : st;
-  const uint32_t* perm = nullptr;
+  static const int sub_env = getenv("RT_SUBFRAMES") ? atoi(getenv("RT_SUBFRAMES")) : 2;
+  static const uint64_t sub_min_slots = getenv("RT_SUBFRAMES_MIN") ? strtoull(getenv("RT_SUBFRAMES_MIN"), nullptr, 10) : (12ull << 20);
+  const bool may_sort = accel != ACCEL_BRUTE && sort_from <= (int)U.max_bounce && sort_from <= sort_to;
+  const bool wave = accel == ACCEL_WIDE && wave_on && rq.scene.tlas == nullptr;
+  const int nsub = (sub_env >= 2 && nslots >= sub_min_slots && !may_sort && !wave)
+                       ? (int)std::min<uint32_t>((uint32_t)std::min(sub_env, RT_MAX_SUB), U.n_local_tiles) : 1;
+
+  SubCtx ctx[RT_MAX_SUB];
+  {
+    const uint64_t tile_slots = (uint64_t)U.tile_w * U.tile_h * U.spp;
+    for (int k = 0; k < nsub; k++) {
+      SubCtx& c = ctx[k];
+      c.sb = &p->sub[k];
+      c.st = k == 0 ? st : c.sb->own;
+      c.sst = shadow_async ? c.sb->aux : c.st;
+      const uint64_t off = (uint64_t)U.n_local_tiles * k / nsub * tile_slots;
+      const uint64_t end = (uint64_t)U.n_local_tiles * (k + 1) / nsub * tile_slots;
+      c.slot_base = (uint32_t)off;
+      c.nslots = (uint32_t)(end - off);
+      for (int i = 0; i < 2; i++) { c.rayO[i] = p->rayO[i] + off; c.rayD[i] = p->rayD[i] + off; }
+      c.hits = p->hits + off; c.qMiss = p->qMiss + off; c.qDiff = p->qDiff + off; c.qSpec = p->qSpec + off;
+      c.shadowQ = p->shadowQ + 3 * off;
+      c.cnt = p->cnt + (size_t)k * p->cnt_blocks * C_STRIDE;
+    }
+  }
   uint64_t launches = 0;
   RT_CUDA_TRY(cudaEventRecord(p->ev[0], st), err);
-  RT_CUDA_TRY(cudaMemsetAsync(p->cnt, 0, p->cnt_blocks * C_STRIDE * sizeof(uint32_t), st), err);
+  RT_CUDA_TRY(cudaMemsetAsync(p->cnt, 0, (size_t)nsub * p->cnt_blocks * C_STRIDE * sizeof(uint32_t), st), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
-  k_raygen<<<stride_blocks(nslots, 256), 256, 0, st>>>(rq.scene, U, (uint32_t)nslots, p->rayO[0], p->rayD[0], p->sample, p->cnt,
-                                                       rq.want_primary ? rq.d_primary : nullptr);
-  launches++;
-  int cur = 0;
-  uint32_t last_bounce = 0;
-  for (uint32_t j = 0; j <= U.max_bounce; j++) {
-    uint32_t* cj = p->cnt + (size_t)j * C_STRIDE;
-    uint32_t* cn = p->cnt + (size_t)(j + 1) * C_STRIDE;
-    rt_hit* prim = (j == 0 && rq.want_primary) ? rq.d_primary : nullptr;
-#define CALL_TRACE(A, C)                                                                                            \
-  {                                                                                                                 \
-    static int blocks = 0;                                                                                          \
-    if (!blocks) blocks = persistent_blocks(k_trace<A, C>, TRACE_THREADS);                                          \
-    k_trace<A, C><<<blocks, TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->rayO[cur], p->rayD[cur], p->hits, p->qMiss, \
-                                                    p->qDiff, p->qSpec, prim, p->stats64, refill_t, tri_t, perm);   \
+  if (nsub > 1) {
+    RT_CUDA_TRY(cudaEventRecord(p->start, st), err);
+    for (int k = 1; k < nsub; k++) RT_CUDA_TRY(cudaStreamWaitEvent(ctx[k].st, p->start, 0), err);
   }
-    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 0], st), err);
-    const bool wave = accel == ACCEL_WIDE && wave_on && rq.scene.tlas == nullptr;
+  for (int k = 0; k < nsub; k++) {
+    SubCtx& c = ctx[k];
+    k_raygen<<<stride_blocks(c.nslots, 256), 256, 0, c.st>>>(rq.scene, U, c.slot_base, c.nslots, c.rayO[0], c.rayD[0], p->sample,
+                                                             c.cnt, rq.want_primary ? rq.d_primary : nullptr);
+    launches++;
+  }
+  // one bounce of one sub-frame, enqueued without waiting for anything
+  auto enqueue_bounce = [&](SubCtx& c, uint32_t j) -> int {
+    FramePipeline::Sub& sb = *c.sb;
+    cudaStream_t cs = c.st, sst = c.sst;
+    const int cur = c.cur;
+    uint32_t* cj = c.cnt + (size_t)j * C_STRIDE;
+    uint32_t* cn = c.cnt + (size_t)(j + 1) * C_STRIDE;
+    rt_hit* prim = (j == 0 && rq.want_primary) ? rq.d_primary : nullptr;
+    const uint32_t* perm = c.perm;
+#define CALL_TRACE(A, C)                                                                                          \
+  {                                                                                                               \
+    static int blocks = 0;                                                                                        \
+    if (!blocks) blocks = persistent_blocks(k_trace<A, C>, TRACE_THREADS);                                        \
+    k_trace<A, C><<<blocks, TRACE_THREADS, 0, cs>>>(rq.scene, U, cj, c.rayO[cur], c.rayD[cur], c.hits, c.qMiss,   \
+                                                    c.qDiff, c.qSpec, prim, p->stats64, refill_t, tri_t, perm);   \
+  }
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 0], cs), err);
     if (wave) {
       static int wb[2] = {0, 0};
       if (!wb[0]) { wb[0] = persistent_blocks(k_trace_wave<false>, TRACE_THREADS); wb[1] = persistent_blocks(k_trace_wave<true>, TRACE_THREADS); }
-      if (counting) k_trace_wave<true><<<wb[1], TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->rayO[cur], p->rayD[cur], p->hits, p->qMiss, p->qDiff, p->qSpec, prim, p->stats64, wave_refill, wave_tri, perm);
-      else k_trace_wave<false><<<wb[0], TRACE_THREADS, 0, st>>>(rq.scene, U, cj, p->rayO[cur], p->rayD[cur], p->hits, p->qMiss, p->qDiff, p->qSpec, prim, p->stats64, wave_refill, wave_tri, perm);
+      if (counting) k_trace_wave<true><<<wb[1], TRACE_THREADS, 0, cs>>>(rq.scene, U, cj, c.rayO[cur], c.rayD[cur], c.hits, c.qMiss, c.qDiff, c.qSpec, prim, p->stats64, wave_refill, wave_tri, perm);
+      else k_trace_wave<false><<<wb[0], TRACE_THREADS, 0, cs>>>(rq.scene, U, cj, c.rayO[cur], c.rayD[cur], c.hits, c.qMiss, c.qDiff, c.qSpec, prim, p->stats64, wave_refill, wave_tri, perm);
     } else
     RT_DISPATCH_ACCEL(accel, counting, CALL_TRACE);
-    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 1], st), err);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 1], cs), err);
 #undef CALL_TRACE
-    k_shade_miss<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qMiss, p->rayO[cur], p->rayD[cur], p->sample);
-    if (shadow_async && j > 0) RT_CUDA_TRY(cudaStreamWaitEvent(st, p->sev[2 * (j - 1) + 1], 0), err);
-    k_shade_diffuse<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, p->qDiff, p->rayO[cur], p->rayD[cur], p->hits, p->shadowQ,
-                                                    p->sample);
+    k_shade_miss<<<sm_count() * 8, 256, 0, cs>>>(rq.scene, cj, c.qMiss, c.rayO[cur], c.rayD[cur], p->sample);
+    if (shadow_async && j > 0) RT_CUDA_TRY(cudaStreamWaitEvent(cs, sb.sev[2 * (j - 1) + 1], 0), err);
+    k_shade_diffuse<<<sm_count() * 8, 256, 0, cs>>>(rq.scene, cj, c.qDiff, c.rayO[cur], c.rayD[cur], c.hits, c.shadowQ, p->sample);
     if (shadow_async) {
-      RT_CUDA_TRY(cudaEventRecord(p->sev[2 * j], st), err);
-      RT_CUDA_TRY(cudaStreamWaitEvent(sst, p->sev[2 * j], 0), err);
+      RT_CUDA_TRY(cudaEventRecord(sb.sev[2 * j], cs), err);
+      RT_CUDA_TRY(cudaStreamWaitEvent(sst, sb.sev[2 * j], 0), err);
     }
 #define CALL_SHADOW(A, C)                                                                                 \
   {                                                                                                       \
     static int blocks = 0;                                                                                \
     if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
-    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, refill_t, tri_t); \
+    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, refill_t, tri_t); \
   }
-    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 2], sst), err);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 2], sst), err);
     if (wave) {
       static int wb[2] = {0, 0};
       if (!wb[0]) { wb[0] = persistent_blocks(k_shadow_wave<false>, TRACE_THREADS); wb[1] = persistent_blocks(k_shadow_wave<true>, TRACE_THREADS); }
-      if (counting) k_shadow_wave<true><<<wb[1], TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
-      else k_shadow_wave<false><<<wb[0], TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, p->shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
+      if (counting) k_shadow_wave<true><<<wb[1], TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
+      else k_shadow_wave<false><<<wb[0], TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, wave_refill, wave_tri);
     } else
     RT_DISPATCH_ACCEL(accel, counting, CALL_SHADOW);
-    RT_CUDA_TRY(cudaEventRecord(p->kev[4 * j + 3], sst), err);
-    if (shadow_async) RT_CUDA_TRY(cudaEventRecord(p->sev[2 * j + 1], sst), err);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 3], sst), err);
+    if (shadow_async) RT_CUDA_TRY(cudaEventRecord(sb.sev[2 * j + 1], sst), err);
 #undef CALL_SHADOW
     launches += 4;
-    last_bounce = j;
+    c.last_bounce = j;
     if (j < U.max_bounce) {
-      const bool sorting = accel != ACCEL_BRUTE && (int)(j + 1) >= sort_from && (int)(j + 1) <= sort_to;
-      k_shade_spec<<<sm_count() * 8, 256, 0, st>>>(rq.scene, cj, cn, p->qSpec, p->rayO[cur], p->rayD[cur], p->hits,
-                                                   p->rayO[cur ^ 1], p->rayD[cur ^ 1], sorting ? p->sortK[0] : nullptr,
+      const bool sorting = may_sort && (int)(j + 1) >= sort_from && (int)(j + 1) <= sort_to;
+      k_shade_spec<<<sm_count() * 8, 256, 0, cs>>>(rq.scene, cj, cn, c.qSpec, c.rayO[cur], c.rayD[cur], c.hits, c.rayO[cur ^ 1],
+                                                   c.rayD[cur ^ 1], sorting ? p->sortK[0] : nullptr,
                                                    sorting ? p->sortV[0] : nullptr, sort_bits);
       launches++;
-      cur ^= 1;
-      perm = nullptr;
-      if (sorting) {  // reorder the next bounce's rays; the count stays on the device
-        int rc2 = sort_pairs_u32(p->sortK[0], p->sortK[1], p->sortV[0], p->sortV[1], p->cap, cn + C_NRAY, sort_bits, p->sortH, st, err);
+      c.cur ^= 1;
+      c.perm = nullptr;
+      if (sorting) {  // reorder the next bounce's rays; the count stays on the device (single sub-frame only)
+        int rc2 = sort_pairs_u32(p->sortK[0], p->sortK[1], p->sortV[0], p->sortV[1], p->cap, cn + C_NRAY, sort_bits, p->sortH, cs, err);
         if (rc2 != RT_OK) return rc2;
         launches += sort_launches(sort_bits);
-        perm = p->sortV[0];
+        c.perm = p->sortV[0];
       }
       // Deep bounce limits (MAX_BOUNCE_COUNT 63): stop as soon as no ray survives.  The count
-      // travels to pinned memory behind the bounce; bounces 1-8 only look at counts
-      // that have already landed (no stall), deeper ones wait for theirs.
-      RT_CUDA_TRY(cudaMemcpyAsync(&p->h_alive[j + 1], cn + C_NRAY, sizeof(uint32_t), cudaMemcpyDeviceToHost, st), err);
-      RT_CUDA_TRY(cudaEventRecord(p->aev[j + 1], st), err);
-      if (j + 1 > 8) { RT_CUDA_TRY(cudaEventSynchronize(p->aev[j + 1]), err); }
-      bool dead = false;
-      for (uint32_t k = 1; k <= j + 1 && !dead; k++)
-        dead = cudaEventQuery(p->aev[k]) == cudaSuccess && p->h_alive[k] == 0u;
-      if (dead) break;
+      // travels to pinned memory behind the bounce; bounces 1-8 only look at counts that have
+      // already landed (no stall), deeper ones wait for theirs.
+      RT_CUDA_TRY(cudaMemcpyAsync(&sb.h_alive[j + 1], cn + C_NRAY, sizeof(uint32_t), cudaMemcpyDeviceToHost, cs), err);
+      RT_CUDA_TRY(cudaEventRecord(sb.aev[j + 1], cs), err);
+      if (j + 1 > 8) { RT_CUDA_TRY(cudaEventSynchronize(sb.aev[j + 1]), err); }
+      for (uint32_t k = 1; k <= j + 1 && !c.dead; k++)
+        c.dead = cudaEventQuery(sb.aev[k]) == cudaSuccess && sb.h_alive[k] == 0u;
+    }
+    return RT_OK;
+  };
+  for (uint32_t j = 0; j <= U.max_bounce; j++) {
+    bool any = false;
+    for (int k = 0; k < nsub; k++) {
+      if (ctx[k].dead) continue;
+      rc = enqueue_bounce(ctx[k], j);
+      if (rc != RT_OK) return rc;
+      any = any || !ctx[k].dead;
+    }
+    if (!any) break;
+  }
+  // join: every sub-frame's shadow rays, then sub-frame 1 into the caller's stream
+  for (int k = nsub - 1; k >= 0; k--) {
+    SubCtx& c = ctx[k];
+    if (shadow_async) RT_CUDA_TRY(cudaStreamWaitEvent(c.st, c.sb->sev[2 * c.last_bounce + 1], 0), err);
+    if (k > 0) {
+      RT_CUDA_TRY(cudaEventRecord(c.sb->done, c.st), err);
+      RT_CUDA_TRY(cudaStreamWaitEvent(st, c.sb->done, 0), err);
     }
   }
-  if (shadow_async) RT_CUDA_TRY(cudaStreamWaitEvent(st, p->sev[2 * last_bounce + 1], 0), err);
   if (rq.d_out) {
     k_resolve<<<stride_blocks(npix, 256), 256, 0, st>>>(U, (uint32_t)npix, p->sample, rq.d_out, rq.output_format);
     launches++;
@@ -880,52 +974,58 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   RT_CUDA_TRY(cudaEventRecord(p->ev[1], st), err);
   RT_CUDA_TRY(cudaGetLastError(), err);
   // counters -> stats (also the synchronisation point of the frame)
-  p->h_cnt.resize(p->cnt_blocks * C_STRIDE);
+  const size_t cnt_words = p->cnt_blocks * C_STRIDE;
+  std::vector<uint32_t> h_all((size_t)nsub * cnt_words);
   unsigned long long h64[8];
-  RT_CUDA_TRY(cudaMemcpyAsync(p->h_cnt.data(), p->cnt, p->h_cnt.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), err);
+  RT_CUDA_TRY(cudaMemcpyAsync(h_all.data(), p->cnt, h_all.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), err);
   RT_CUDA_TRY(cudaMemcpyAsync(h64, p->stats64, sizeof h64, cudaMemcpyDeviceToHost, st), err);
   RT_CUDA_TRY(cudaStreamSynchronize(st), err);
+  p->h_cnt.assign(cnt_words, 0u);
+  for (int k = 0; k < nsub; k++)
+    for (size_t i = 0; i < cnt_words; i++) p->h_cnt[i] += h_all[(size_t)k * cnt_words + i];
   if (stats) {
     float ms = 0.f;
     cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]);
     stats->frame_ms = ms;
-    double tr = 0.0, sh = 0.0;
-    // trace_ms = the closest-hit launches; shadow_ms = the part of the shadow launches that is not
-    // hidden behind one of them (they run on a second stream), so trace_ms + shadow_ms is the time
-    // during which a traversal kernel was running: the union of all launch intervals
-    std::vector<std::pair<float, float>> iv;
-    for (uint32_t j = 0; j <= last_bounce; j++) {
-      float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
-      cudaEventElapsedTime(&a0, p->ev[0], p->kev[4 * j + 0]);
-      cudaEventElapsedTime(&a1, p->ev[0], p->kev[4 * j + 1]);
-      cudaEventElapsedTime(&b0, p->ev[0], p->kev[4 * j + 2]);
-      cudaEventElapsedTime(&b1, p->ev[0], p->kev[4 * j + 3]);
-      tr += a1 - a0;
-      iv.push_back({a0, a1});
-      iv.push_back({b0, b1});
-    }
-    std::sort(iv.begin(), iv.end());
-    double uni = 0.0;
-    float cur_end = -1.0f;
-    for (auto& x : iv) {
-      const float s0 = std::max(x.first, cur_end);
-      if (x.second > s0) { uni += x.second - s0; cur_end = x.second; }
-    }
-    sh = std::max(0.0, uni - tr);
-    stats->trace_ms = tr;
-    static const bool dbg = getenv("RT_DEBUG_BOUNCES") != nullptr;
-    if (dbg) {
-      for (uint32_t j = 0; j <= last_bounce; j++) {
-        float a = 0.f, b = 0.f;
-        cudaEventElapsedTime(&a, p->kev[4 * j + 0], p->kev[4 * j + 1]);
-        cudaEventElapsedTime(&b, p->kev[4 * j + 2], p->kev[4 * j + 3]);
-        const uint32_t* c = &p->h_cnt[(size_t)j * C_STRIDE];
-        fprintf(stderr, "bounce %u: trace %.3f ms shadow %.3f ms  rays %u miss %u diff %u spec %u shadow %u\n", j, a, b,
-                c[C_NRAY], c[C_NMISS], c[C_NDIFF], c[C_NSPEC], c[C_NSHADOW]);
+    uint32_t last_bounce = 0;
+    for (int k = 0; k < nsub; k++) last_bounce = std::max(last_bounce, ctx[k].last_bounce);
+    // trace_ms = time during which a closest-hit launch was running, shadow_ms = the part of the
+    // shadow launches not hidden behind one (they run on other streams), so trace_ms + shadow_ms is
+    // the time a traversal kernel was running: unions of the launch intervals of all sub-frames
+    auto union_ms = [](std::vector<std::pair<float, float>>& iv) {
+      std::sort(iv.begin(), iv.end());
+      double uni = 0.0;
+      float cur_end = -1.0f;
+      for (auto& x : iv) {
+        const float s0 = std::max(x.first, cur_end);
+        if (x.second > s0) { uni += x.second - s0; cur_end = x.second; }
       }
-    }
+      return uni;
+    };
+    std::vector<std::pair<float, float>> iv_trace, iv_all;
+    static const bool dbg = getenv("RT_DEBUG_BOUNCES") != nullptr;
+    for (int k = 0; k < nsub; k++)
+      for (uint32_t j = 0; j <= ctx[k].last_bounce; j++) {
+        const auto& kev = ctx[k].sb->kev;
+        float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+        cudaEventElapsedTime(&a0, p->ev[0], kev[4 * j + 0]);
+        cudaEventElapsedTime(&a1, p->ev[0], kev[4 * j + 1]);
+        cudaEventElapsedTime(&b0, p->ev[0], kev[4 * j + 2]);
+        cudaEventElapsedTime(&b1, p->ev[0], kev[4 * j + 3]);
+        iv_trace.push_back({a0, a1});
+        iv_all.push_back({a0, a1});
+        iv_all.push_back({b0, b1});
+        if (dbg) {
+          const uint32_t* c = &h_all[(size_t)k * cnt_words + (size_t)j * C_STRIDE];
+          fprintf(stderr, "sub %d bounce %u: trace %.3f..%.3f ms shadow %.3f..%.3f ms  rays %u miss %u diff %u spec %u shadow %u\n", k,
+                  j, a0, a1, b0, b1, c[C_NRAY], c[C_NMISS], c[C_NDIFF], c[C_NSPEC], c[C_NSHADOW]);
+        }
+      }
+    const double tr = union_ms(iv_trace), uni = union_ms(iv_all);
+    const double sh = std::max(0.0, uni - tr);
+    stats->trace_ms = tr;
     stats->shadow_ms = sh;
-    stats->shade_ms = std::max(0.0, (double)ms - tr - sh);   // (trace and shadow intervals may overlap)
+    stats->shade_ms = std::max(0.0, (double)ms - tr - sh);
     // primary traces = rays traversed + rays the top level answered in k_raygen
     stats->rays_primary = (uint64_t)p->h_cnt[C_NRAY] + p->h_cnt[C_NCULL];
     stats->rays_secondary = stats->rays_shadow = stats->n_hit = 0;

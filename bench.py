@@ -233,7 +233,7 @@ def main():
                                     shard_index=rank if sharded else 0, shard_count=world if sharded else 1)
     npix_local = int(rt.rt_lib().rt_frame_shard_pixels(C.byref(p_compact))) if sharded else W * H
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
-    launches = {"n": 0}
+    launches = {"n": 0, "frames": 0}   # n: kernels around the frame (signal / wait / assemble); frames: frames rendered
     host = torch.zeros((H, W, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
 
     # ---- how the tiles reach rank 0 -----------------------------------------------------------------
@@ -274,9 +274,12 @@ def main():
         gathered = torch.zeros((world, npix_local, 4), dtype=torch.uint8, device=dev) if (sharded and rank == 0) else None
         frame = torch.zeros((H, W, 4), dtype=torch.uint8, device=dev) if (sharded and rank == 0) else None
 
+    frame_no = {"n": 0}
+    stream_handle = torch.cuda.current_stream().cuda_stream
+
     def nccl_step(p, loc, gat, frm):
         scene.render_into(cam, p, loc.data_ptr())
-        launches["n"] += scene.stats()["kernel_launches"]
+        launches["frames"] += 1
         dist.gather(loc, [gat[i] for i in range(world)] if rank == 0 else None, dst=0)
         if rank == 0:
             scene.assemble_shards(p, gat.data_ptr(), frm.data_ptr())
@@ -284,14 +287,19 @@ def main():
 
     def step(to_host):
         if gather == "peer":
-            scene.render_into(cam, p_dev, peer.ptr)   # returns once this rank's stores have completed
-            launches["n"] += scene.stats()["kernel_launches"]
-            dist.barrier()                            # ... and now everybody's have
+            frame_no["n"] += 1
+            scene.render_into(cam, p_dev, peer.ptr)   # this rank's tiles go straight into rank 0's frame
+            launches["frames"] += 1
+            launches["n"] += 1
+            peer.signal(rank, frame_no["n"], stream_handle)          # arrival flag in rank 0's memory, behind the stores
+            if rank == 0:
+                peer.wait(world, frame_no["n"], stream_handle)       # every rank's tiles are in place
+                launches["n"] += 1
         elif gather == "nccl":
             nccl_step(p_dev, local, gathered, frame)
         else:
             scene.render_into(cam, p_dev, local.data_ptr())
-            launches["n"] += scene.stats()["kernel_launches"]
+            launches["frames"] += 1
         if to_host and rank == 0:
             src = frame if sharded else local.view(H, W, 4)
             host.copy_(src, non_blocking=True)
@@ -338,9 +346,10 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    launches["n"] = 0
+    launches["n"] = launches["frames"] = 0
     ms_dev, rays_dev = timed(False, args.steps)
-    n_launch = launches["n"]
+    # rt_stats.kernel_launches of a frame (read outside the timed region: the library works the stats out on demand)
+    n_launch = launches["n"] + launches["frames"] * scene.stats()["kernel_launches"]
     st_last = scene.stats()
     ms_e2e, rays_e2e = timed(True, args.steps)
     clocks = sampler.stop() if rank == 0 else None
@@ -378,7 +387,7 @@ def main():
     if sharded:
         out["gather"] = {
             "peer": "k_resolve of every rank stores its tiles into rank 0's frame (CUDA IPC mapping, NVLink peer stores), "
-                    "then one barrier; no gather collective, no de-interleave pass",
+                    "then one arrival flag per rank that rank 0 waits for; no collective, no de-interleave pass",
             "nccl": "torch.distributed.gather (NCCL) of the compact tile buffers + rt_assemble_shards"}[gather]
         out["gather_mode"] = gather
         if gather_verified is not None:

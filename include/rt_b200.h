@@ -256,6 +256,16 @@ int rt_assemble_shards(void* scene, const rt_frame_params* params, const void* g
 typedef struct rt_ipc_handle { unsigned char opaque[64]; } rt_ipc_handle;
 int rt_peer_frame_create(int device_id, uint64_t bytes, void** frame_out, rt_ipc_handle* handle_out);
 int rt_peer_frame_open(int device_id, const rt_ipc_handle* handle, void** frame_out);
+/* Arrival flags instead of a barrier collective (they live behind the frame, in the owner's
+ * memory).  Every rank, after rt_render_frame into the frame: rt_peer_frame_signal(..., rank,
+ * frame_number, stream) - one store over NVLink, ordered behind the tile stores.  The owner:
+ * rt_peer_frame_wait(..., n_ranks, frame_number, timeout_ms, stream) returns when all n_ranks
+ * flags have reached frame_number (wrap-safe compare), RT_ERR_CUDA after timeout_ms (0 = 2000).
+ * frame_bytes = the size given to rt_peer_frame_create.  The ranks must not start storing frame
+ * n+1 before the owner has consumed frame n (double-buffer or synchronise outside). */
+int rt_peer_frame_signal(int device_id, void* frame, uint64_t frame_bytes, uint32_t rank, uint32_t value, void* stream);
+int rt_peer_frame_wait(int device_id, void* frame, uint64_t frame_bytes, uint32_t n_ranks, uint32_t value,
+                       uint32_t timeout_ms, void* stream);
 int rt_peer_frame_close(int device_id, void* frame);     /* peer side */
 int rt_peer_frame_destroy(int device_id, void* frame);   /* owner side */
 

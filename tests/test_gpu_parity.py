@@ -355,6 +355,15 @@ def test_shards_stored_in_frame_equal_the_full_frame(gpu_rt):
             assert np.array_equal(now[seen], full[seen])
             assert np.all(now[~seen] == 7)
         assert seen.all()
+        # arrival flags behind the frame: three ranks report frame 5, the owner's wait for three returns,
+        # a wait for a fourth that never reports times out with an error
+        for r in range(3):
+            pf.signal(r, 5)
+        pf.wait(3, 5)
+        pf.wait(3, 4)          # an older frame number is already satisfied (wrap-safe compare)
+        with pytest.raises(rt.RtError):
+            pf.wait(4, 5, timeout_ms=30)
+        assert np.array_equal(frame.cpu().numpy(), full)      # the flags are not part of the frame
         del frame
         pf.release()
     # host output of a partial frame is refused

@@ -398,6 +398,8 @@ def rt_lib():
         L.rt_assemble_shards.argtypes = [C.c_void_p, C.POINTER(FrameParams), C.c_void_p, C.c_void_p]
         L.rt_peer_frame_create.argtypes = [C.c_int, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(IpcHandle)]
         L.rt_peer_frame_open.argtypes = [C.c_int, C.POINTER(IpcHandle), C.POINTER(C.c_void_p)]
+        L.rt_peer_frame_signal.argtypes = [C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]
+        L.rt_peer_frame_wait.argtypes = [C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
         L.rt_peer_frame_close.argtypes = [C.c_int, C.c_void_p]
         L.rt_peer_frame_destroy.argtypes = [C.c_int, C.c_void_p]
         L.rt_primary_hits.argtypes = [C.c_void_p, C.POINTER(CameraVectors), C.POINTER(FrameParams), C.c_void_p]
@@ -525,6 +527,16 @@ class PeerFrame:
 
     def handle_bytes(self) -> bytes:
         return bytes(self._handle.opaque)
+
+    def signal(self, rank: int, value: int, stream: int = 0):
+        """This rank's tiles of frame `value` are in place (ordered behind the render on `stream`)."""
+        _check(rt_lib().rt_peer_frame_signal(self.device_id, C.c_void_p(self.ptr), self.nbytes, rank, value & 0xFFFFFFFF,
+                                             C.c_void_p(stream)))
+
+    def wait(self, n_ranks: int, value: int, stream: int = 0, timeout_ms: int = 2000):
+        """Owner: block until all n_ranks flags have reached `value`."""
+        _check(rt_lib().rt_peer_frame_wait(self.device_id, C.c_void_p(self.ptr), self.nbytes, n_ranks, value & 0xFFFFFFFF,
+                                           timeout_ms, C.c_void_p(stream)))
 
     @property
     def __cuda_array_interface__(self):   # lets torch / cupy view the frame as uint8[nbytes]

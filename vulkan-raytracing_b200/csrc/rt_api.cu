@@ -387,13 +387,40 @@ int rt_generate_normals(int device_id, float* vertices, uint32_t nv, const uint3
 }
 
 // ---- frame buffers other processes can store into (CUDA IPC over NVLink peer access) ----------
+static const size_t PEER_FLAG_BYTES = 4096;   // 1024 ranks
+static size_t peer_flag_offset(uint64_t frame_bytes) { return (size_t)((frame_bytes + 255) & ~(uint64_t)255); }
+
+// "my tiles of frame `value` are in place": ordered behind the resolve kernel's stores on the same stream
+__global__ void k_peer_signal(uint32_t* flags, uint32_t rank, uint32_t value) {
+  __threadfence_system();
+  *(volatile uint32_t*)&flags[rank] = value;
+  __threadfence_system();
+}
+
+// owner side: spin until every rank's flag has reached `value` (or the time-out passes: status = 1)
+__global__ void k_peer_wait(const uint32_t* flags, uint32_t n_ranks, uint32_t value, unsigned long long timeout_ns,
+                            uint32_t* status) {
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+  for (uint32_t r = threadIdx.x; r < n_ranks; r += blockDim.x) {
+    while ((int32_t)(*(volatile const uint32_t*)&flags[r] - value) < 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      if (t - t0 > timeout_ns) { *status = 1u; break; }
+      __nanosleep(200);
+    }
+  }
+  __threadfence_system();
+}
+
 int rt_peer_frame_create(int device_id, uint64_t bytes, void** frame_out, rt_ipc_handle* handle_out) {
   if (!frame_out || !handle_out || bytes == 0) return fail(RT_ERR_INVALID_ARGUMENT, "null argument or empty frame");
   static_assert(sizeof(cudaIpcMemHandle_t) <= sizeof(rt_ipc_handle), "handle size");
   if (rt_device_count() < 1) return fail(RT_ERR_NO_DEVICE, "no CUDA device");
   RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
   void* d = nullptr;
-  RT_CUDA_TRY(cudaMalloc(&d, bytes), g_err);
+  RT_CUDA_TRY(cudaMalloc(&d, peer_flag_offset(bytes) + PEER_FLAG_BYTES), g_err);   // frame, then one arrival flag per rank
+  RT_CUDA_TRY(cudaMemset((char*)d + peer_flag_offset(bytes), 0, PEER_FLAG_BYTES), g_err);
   cudaIpcMemHandle_t h;
   cudaError_t e = cudaIpcGetMemHandle(&h, d);
   if (e != cudaSuccess) {
@@ -415,6 +442,31 @@ int rt_peer_frame_open(int device_id, const rt_ipc_handle* handle, void** frame_
   void* d = nullptr;
   RT_CUDA_TRY(cudaIpcOpenMemHandle(&d, h, cudaIpcMemLazyEnablePeerAccess), g_err);
   *frame_out = d;
+  return RT_OK;
+}
+
+int rt_peer_frame_signal(int device_id, void* frame, uint64_t frame_bytes, uint32_t rank, uint32_t value, void* stream) {
+  if (!frame || rank >= PEER_FLAG_BYTES / 4) return fail(RT_ERR_INVALID_ARGUMENT, "bad peer frame or rank");
+  RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
+  k_peer_signal<<<1, 1, 0, (cudaStream_t)stream>>>((uint32_t*)((char*)frame + peer_flag_offset(frame_bytes)), rank, value);
+  RT_CUDA_TRY(cudaGetLastError(), g_err);
+  return RT_OK;
+}
+
+int rt_peer_frame_wait(int device_id, void* frame, uint64_t frame_bytes, uint32_t n_ranks, uint32_t value, uint32_t timeout_ms,
+                       void* stream) {
+  if (!frame || n_ranks == 0 || n_ranks > PEER_FLAG_BYTES / 4) return fail(RT_ERR_INVALID_ARGUMENT, "bad peer frame or rank count");
+  RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
+  static uint32_t* d_status = nullptr;
+  if (!d_status) RT_CUDA_TRY(cudaMalloc(&d_status, sizeof(uint32_t)), g_err);
+  cudaStream_t st = (cudaStream_t)stream;
+  RT_CUDA_TRY(cudaMemsetAsync(d_status, 0, sizeof(uint32_t), st), g_err);
+  k_peer_wait<<<1, 128, 0, st>>>((const uint32_t*)((char*)frame + peer_flag_offset(frame_bytes)), n_ranks, value,
+                                 (unsigned long long)(timeout_ms ? timeout_ms : 2000u) * 1000000ull, d_status);
+  uint32_t status = 0;
+  RT_CUDA_TRY(cudaMemcpyAsync(&status, d_status, sizeof status, cudaMemcpyDeviceToHost, st), g_err);
+  RT_CUDA_TRY(cudaStreamSynchronize(st), g_err);
+  if (status) return fail(RT_ERR_CUDA, "rt_peer_frame_wait: a rank did not deliver its tiles in time");
   return RT_OK;
 }
 
@@ -496,6 +548,7 @@ int rt_trace_rays(void* scene, uint64_t n, const float* origins, const float* di
 
 int rt_get_stats(void* scene, rt_stats* out) {
   if (!scene || !out) return fail(RT_ERR_INVALID_ARGUMENT, "null argument");
+  pipeline_frame_stats(((Scene*)scene)->pipe, &((Scene*)scene)->stats);
   *out = ((Scene*)scene)->stats;
   return RT_OK;
 }

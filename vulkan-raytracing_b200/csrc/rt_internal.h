@@ -65,6 +65,8 @@ struct FrameRequest {
   rt_hit* d_primary;     // device, n_slots*spp records in (y*w+x)*spp+s order, may be null
 };
 int pipeline_render(FramePipeline*, const FrameRequest&, cudaStream_t, rt_stats* stats, std::string& err);
+// fills the frame fields of rt_stats for the last pipeline_render (event arithmetic on demand)
+void pipeline_frame_stats(FramePipeline*, rt_stats* stats);
 int pipeline_trace_batch(FramePipeline*, const SceneDev&, uint64_t n, const float* d_o, const float* d_d, float tmin,
                          float tmax, bool any_hit, bool counting, rt_hit* d_out, cudaStream_t, rt_stats* stats,
                          std::string& err);

@@ -670,6 +670,13 @@ struct FramePipeline {
     cudaEvent_t done = nullptr;
   } sub[RT_MAX_SUB];
   cudaEvent_t start = nullptr;
+  // what pipeline_frame_stats needs of the last frame (the event arithmetic is done on demand)
+  int last_nsub = 0;
+  uint32_t last_bounce[RT_MAX_SUB] = {0, 0, 0, 0};
+  uint64_t last_launches = 0;
+  std::vector<uint32_t> h_all;
+  unsigned long long h64[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  bool stats_pending = false;
 };
 
 FramePipeline* pipeline_create() { return new FramePipeline(); }
@@ -973,22 +980,38 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   }
   RT_CUDA_TRY(cudaEventRecord(p->ev[1], st), err);
   RT_CUDA_TRY(cudaGetLastError(), err);
-  // counters -> stats (also the synchronisation point of the frame)
+  // counters to the host (also the synchronisation point of the frame); the stage times are
+  // worked out from the events when somebody asks (pipeline_frame_stats)
   const size_t cnt_words = p->cnt_blocks * C_STRIDE;
-  std::vector<uint32_t> h_all((size_t)nsub * cnt_words);
-  unsigned long long h64[8];
-  RT_CUDA_TRY(cudaMemcpyAsync(h_all.data(), p->cnt, h_all.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), err);
-  RT_CUDA_TRY(cudaMemcpyAsync(h64, p->stats64, sizeof h64, cudaMemcpyDeviceToHost, st), err);
+  p->h_all.resize((size_t)nsub * cnt_words);
+  RT_CUDA_TRY(cudaMemcpyAsync(p->h_all.data(), p->cnt, p->h_all.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), err);
+  RT_CUDA_TRY(cudaMemcpyAsync(p->h64, p->stats64, sizeof p->h64, cudaMemcpyDeviceToHost, st), err);
   RT_CUDA_TRY(cudaStreamSynchronize(st), err);
+  p->last_nsub = nsub;
+  for (int k = 0; k < nsub; k++) p->last_bounce[k] = ctx[k].last_bounce;
+  p->last_launches = launches;
+  p->stats_pending = true;
+  (void)stats;
+  return RT_OK;
+}
+
+// Frame fields of rt_stats for the last pipeline_render (no-op if they are already up to date).
+void pipeline_frame_stats(FramePipeline* p, rt_stats* stats) {
+  if (!p || !stats || !p->stats_pending) return;
+  p->stats_pending = false;
+  const int nsub = p->last_nsub;
+  const size_t cnt_words = p->cnt_blocks * C_STRIDE;
+  const std::vector<uint32_t>& h_all = p->h_all;
+  const unsigned long long* h64 = p->h64;
   p->h_cnt.assign(cnt_words, 0u);
   for (int k = 0; k < nsub; k++)
     for (size_t i = 0; i < cnt_words; i++) p->h_cnt[i] += h_all[(size_t)k * cnt_words + i];
-  if (stats) {
+  {
     float ms = 0.f;
     cudaEventElapsedTime(&ms, p->ev[0], p->ev[1]);
     stats->frame_ms = ms;
     uint32_t last_bounce = 0;
-    for (int k = 0; k < nsub; k++) last_bounce = std::max(last_bounce, ctx[k].last_bounce);
+    for (int k = 0; k < nsub; k++) last_bounce = std::max(last_bounce, p->last_bounce[k]);
     // trace_ms = time during which a closest-hit launch was running, shadow_ms = the part of the
     // shadow launches not hidden behind one (they run on other streams), so trace_ms + shadow_ms is
     // the time a traversal kernel was running: unions of the launch intervals of all sub-frames
@@ -1005,8 +1028,8 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     std::vector<std::pair<float, float>> iv_trace, iv_all;
     static const bool dbg = getenv("RT_DEBUG_BOUNCES") != nullptr;
     for (int k = 0; k < nsub; k++)
-      for (uint32_t j = 0; j <= ctx[k].last_bounce; j++) {
-        const auto& kev = ctx[k].sb->kev;
+      for (uint32_t j = 0; j <= p->last_bounce[k]; j++) {
+        const auto& kev = p->sub[k].kev;
         float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
         cudaEventElapsedTime(&a0, p->ev[0], kev[4 * j + 0]);
         cudaEventElapsedTime(&a1, p->ev[0], kev[4 * j + 1]);
@@ -1040,16 +1063,16 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     }
     stats->nodes_visited = h64[0] + h64[2];
     stats->tris_tested = h64[1] + h64[3];
-    stats->kernel_launches = launches;
+    stats->kernel_launches = p->last_launches;
     stats->ray_state_bytes = 2 * sizeof(float4) + sizeof(uint4) + sizeof(uint32_t);
   }
-  return RT_OK;
 }
 
 int pipeline_trace_batch(FramePipeline* p, const SceneDev& scene, uint64_t n, const float* d_o, const float* d_d,
                          float tmin, float tmax, bool any_hit, bool counting, rt_hit* d_out, cudaStream_t st,
                          rt_stats* stats, std::string& err) {
   if (n == 0) return RT_OK;
+  p->stats_pending = false;   // the stats below replace those of the last frame
   if (!p->stats64) RT_CUDA_TRY(cudaMalloc(&p->stats64, 8 * sizeof(unsigned long long)), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
   const int blocks = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + TRACE_THREADS - 1) / TRACE_THREADS, (uint64_t)sm_count() * 8));

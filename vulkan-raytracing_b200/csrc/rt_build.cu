@@ -110,14 +110,26 @@ __global__ void __launch_bounds__(256) k_refit(BuildArrays a) {
 }
 
 // SAH treelet refinement (rt_build.cuh), one launch per bottom-up round
-__global__ void __launch_bounds__(256) k_treelet_leaves(BuildArrays a, uint32_t* queue, uint32_t* qcount) {
+__global__ void __launch_bounds__(256) k_treelet_leaves(BuildArrays a, uint32_t* queue, uint32_t* qcount, bool fit) {
   for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < a.ntri; j += gridDim.x * blockDim.x)
-    treelet_leaf_arrive(a, j, queue, qcount);
+    treelet_leaf_arrive(a, j, queue, qcount, fit);
 }
-__global__ void __launch_bounds__(128) k_treelet_round(BuildArrays a, const uint32_t* __restrict__ queue, uint32_t count,
-                                                       uint32_t* next_queue, uint32_t* next_count) {
+// dynamic-programming tables in shared memory, entry s of thread t at [s][t]: the threads of a
+// warp walk the subsets in the same order, so every access is one conflict-free row
+static const int TREELET_THREADS = 64;
+struct TreeletSmemTables {
+  float* c;      // -> cost[0][threadIdx.x]
+  uint8_t* p;    // -> part[0][threadIdx.x]
+  __device__ float& cost(int s) { return c[s * TREELET_THREADS]; }
+  __device__ uint8_t& part(int s) { return p[s * TREELET_THREADS]; }
+};
+__global__ void __launch_bounds__(TREELET_THREADS) k_treelet_round(BuildArrays a, const uint32_t* __restrict__ queue, uint32_t count,
+                                                                   uint32_t* next_queue, uint32_t* next_count, bool fit) {
+  __shared__ float s_cost[(1 << TREELET_LEAVES) * TREELET_THREADS];     // 32 KB
+  __shared__ uint8_t s_part[(1 << TREELET_LEAVES) * TREELET_THREADS];   //  8 KB
+  TreeletSmemTables tab{s_cost + threadIdx.x, s_part + threadIdx.x};
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
-    treelet_round_node(a, queue[i], next_queue, next_count);
+    treelet_round_node(a, queue[i], next_queue, next_count, tab, fit);
 }
 
 __global__ void __launch_bounds__(128) k_collapse(BuildArrays a, uint32_t begin, uint32_t end) {
@@ -247,20 +259,25 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
     mark("sort");
     if (ntri > 1) k_karras<<<grid_for(N, 256), 256, 0, stream>>>(a);
     mark("karras");
-    k_refit<<<grid_for(N, 256), 256, 0, stream>>>(a);
-    mark("refit");
     static const int treelet_passes = getenv("RT_TREELET_PASSES") ? atoi(getenv("RT_TREELET_PASSES")) : 1;
-    if (ntri > 2 && refine && treelet_passes > 0) {
+    const bool do_treelets = ntri > 2 && refine && treelet_passes > 0;
+    if (!do_treelets) {   // otherwise the first treelet pass fits the boxes on its way up
+      k_refit<<<grid_for(N, 256), 256, 0, stream>>>(a);
+      mark("refit");
+    }
+    if (do_treelets) {
       RT_CUDA_TRY(tmp.get(&a.cost, 2 * N), err);
       uint32_t* queue[2] = {nullptr, nullptr};
       uint32_t* qcount = nullptr;  // [2]
       RT_CUDA_TRY(tmp.get(&queue[0], N), err);
       RT_CUDA_TRY(tmp.get(&queue[1], N), err);
       RT_CUDA_TRY(tmp.get(&qcount, 2), err);
+      // 5 CTAs x 40 KB of tables per SM
+      cudaFuncSetAttribute(k_treelet_round, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
       for (int pass = 0; pass < treelet_passes; pass++) {
         RT_CUDA_TRY(cudaMemsetAsync(a.flags, 0, N * sizeof(uint32_t), stream), err);
         RT_CUDA_TRY(cudaMemsetAsync(qcount, 0, 2 * sizeof(uint32_t), stream), err);
-        k_treelet_leaves<<<grid_for(N, 256), 256, 0, stream>>>(a, queue[0], qcount);
+        k_treelet_leaves<<<grid_for(N, 256), 256, 0, stream>>>(a, queue[0], qcount, pass == 0);
         mark("treelet leaves");
         int cur = 0;
         for (int round = 0; round < 4096; round++) {
@@ -269,7 +286,7 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
           RT_CUDA_TRY(cudaStreamSynchronize(stream), err);
           if (count == 0) break;
           RT_CUDA_TRY(cudaMemsetAsync(qcount + (cur ^ 1), 0, sizeof(uint32_t), stream), err);
-          k_treelet_round<<<grid_for(count, 128), 128, 0, stream>>>(a, queue[cur], count, queue[cur ^ 1], qcount + (cur ^ 1));
+          k_treelet_round<<<grid_for(count, TREELET_THREADS), TREELET_THREADS, 0, stream>>>(a, queue[cur], count, queue[cur ^ 1], qcount + (cur ^ 1), pass == 0);
           if (dbg && round < 6) mark("treelet round");
           cur ^= 1;
         }

@@ -173,14 +173,52 @@ RT_HD float half_area(float4 lo, float4 hi) {
 // programming over the 2^7 leaf subsets finds the topology with the smallest SAH cost
 //   C(s) = CT * area(s) + min over splits p of C(p) + C(s \ p),   C({leaf}) = subtree cost,
 // and the treelet's inner nodes are rewritten in place (same node ids, root keeps its id, so the
-// parent above is untouched).  One thread per treelet; threads climb from the leaves with the
-// same second-arrival rule as the box fit, so a treelet is only touched after everything below
-// it is final.  Subtrees no longer cover contiguous Morton ranges afterwards.
+// parent above is untouched).  One thread per treelet; a treelet is only touched after everything
+// below it is final (rounds over ready queues on the GPU, second-arrival climb in the serial schedule).  Subtrees no longer cover contiguous Morton ranges afterwards.
 static const int TREELET_LEAVES = 7;
 #define RT_SAH_CT 1.0f   // cost of one inner node visit (two box tests)
 #define RT_SAH_CI 1.3f   // cost of one triangle test
 
-RT_HD void treelet_optimize_node(const BuildArrays& a, int x) {
+// Tables of the dynamic programme: cost (first the area) and chosen split of every leaf subset.
+// The serial schedule keeps them in plain arrays; the GPU kernel keeps them in shared memory,
+// one column per thread (TreeletSmemTables in rt_build.cu) - as per-thread local arrays they are
+// 1.2 KB per thread, far more than L1 holds for a resident warp set, and every one of the ~2000
+// table reads of a treelet went to L2.
+struct TreeletLocalTables {
+  float c[1 << TREELET_LEAVES];
+  uint8_t p[1 << TREELET_LEAVES];
+  RT_HD float& cost(int s) { return c[s]; }
+  RT_HD uint8_t& part(int s) { return p[s]; }
+};
+
+struct Box6 { float lx, ly, lz, hx, hy, hz; };
+RT_HD Box6 box6_empty() { return Box6{3.0e38f, 3.0e38f, 3.0e38f, -3.0e38f, -3.0e38f, -3.0e38f}; }
+RT_HD Box6 box6_of(float4 lo, float4 hi) { return Box6{lo.x, lo.y, lo.z, hi.x, hi.y, hi.z}; }
+RT_HD Box6 box6_join(Box6 a, Box6 b) {
+  return Box6{fminf(a.lx, b.lx), fminf(a.ly, b.ly), fminf(a.lz, b.lz), fmaxf(a.hx, b.hx), fmaxf(a.hy, b.hy), fmaxf(a.hz, b.hz)};
+}
+RT_HD float box6_half_area(Box6 b) {
+  const float dx = b.hx - b.lx, dy = b.hy - b.ly, dz = b.hz - b.lz;
+  return dx * dy + dy * dz + dz * dx;
+}
+
+// area of the union box of every subset whose highest leaf is T, written to tab.cost(s):
+// the box of leaves 0..T-1 selected by the low bits is joined leaf by leaf (fully unrolled, the
+// leaf boxes stay in registers and shared prefixes are computed once)
+template <int T, class Tables>
+RT_HD void treelet_subset_areas(const Box6 (&lb)[TREELET_LEAVES], Tables& tab) {
+#pragma unroll
+  for (int m = 0; m < (1 << T); m++) {
+    Box6 u = lb[T];
+#pragma unroll
+    for (int i = T - 1; i >= 0; i--)
+      if (m & (1 << i)) u = box6_join(u, lb[i]);
+    tab.cost(m | (1 << T)) = box6_half_area(u);
+  }
+}
+
+template <class Tables>
+RT_HD void treelet_optimize_node(const BuildArrays& a, int x, Tables& tab) {
   const int n = (int)a.ntri;
   int leaves[TREELET_LEAVES], inner[TREELET_LEAVES - 1];
   float4 llo[TREELET_LEAVES], lhi[TREELET_LEAVES];
@@ -209,60 +247,59 @@ RT_HD void treelet_optimize_node(const BuildArrays& a, int x) {
     llo[nl] = RT_LDCG(&a.node_lo[leaves[nl]]); lhi[nl] = RT_LDCG(&a.node_hi[leaves[nl]]);
     nl++;
   }
-  float lcost[TREELET_LEAVES];
   float cur = RT_SAH_CT * inner_area;
-  for (int i = 0; i < nl; i++) { lcost[i] = RT_LDCG(&a.cost[leaves[i]]); cur += lcost[i]; }
+  for (int i = 0; i < nl; i++) cur += RT_LDCG(&a.cost[leaves[i]]);
   if (nl < 3) { a.cost[x] = cur; return; }  // two leaves: nothing to rearrange
   const int S = 1 << nl;
-  float area[1 << TREELET_LEAVES], copt[1 << TREELET_LEAVES];
-  uint8_t part[1 << TREELET_LEAVES];
   {
-    // area of the union box of every leaf subset: boxes of the 16 subsets of leaves 0-3 and of
-    // the 8 subsets of leaves 4-6 first, then one union per subset
-    float lob[16][6], hib[8][6];
-    for (int m = 0; m < 16; m++) {
-      float lx = 3.0e38f, ly = 3.0e38f, lz = 3.0e38f, hx = -3.0e38f, hy = -3.0e38f, hz = -3.0e38f;
-      for (int i = 0; i < 4 && i < nl; i++)
-        if (m & (1 << i)) {
-          lx = fminf(lx, llo[i].x); ly = fminf(ly, llo[i].y); lz = fminf(lz, llo[i].z);
-          hx = fmaxf(hx, lhi[i].x); hy = fmaxf(hy, lhi[i].y); hz = fmaxf(hz, lhi[i].z);
-        }
-      lob[m][0] = lx; lob[m][1] = ly; lob[m][2] = lz; lob[m][3] = hx; lob[m][4] = hy; lob[m][5] = hz;
-    }
-    for (int m = 0; m < 8; m++) {
-      float lx = 3.0e38f, ly = 3.0e38f, lz = 3.0e38f, hx = -3.0e38f, hy = -3.0e38f, hz = -3.0e38f;
-      for (int i = 4; i < nl; i++)
-        if (m & (1 << (i - 4))) {
-          lx = fminf(lx, llo[i].x); ly = fminf(ly, llo[i].y); lz = fminf(lz, llo[i].z);
-          hx = fmaxf(hx, lhi[i].x); hy = fmaxf(hy, lhi[i].y); hz = fmaxf(hz, lhi[i].z);
-        }
-      hib[m][0] = lx; hib[m][1] = ly; hib[m][2] = lz; hib[m][3] = hx; hib[m][4] = hy; hib[m][5] = hz;
-    }
-    for (int s = 1; s < S; s++) {
-      const float* a0 = lob[s & 15];
-      const float* a1 = hib[s >> 4];
-      const float dx = fmaxf(a0[3], a1[3]) - fminf(a0[0], a1[0]), dy = fmaxf(a0[4], a1[4]) - fminf(a0[1], a1[1]),
-                  dz = fmaxf(a0[5], a1[5]) - fminf(a0[2], a1[2]);
-      area[s] = dx * dy + dy * dz + dz * dx;
-    }
+    Box6 lb[TREELET_LEAVES];
+#pragma unroll
+    for (int i = 0; i < TREELET_LEAVES; i++) lb[i] = i < nl ? box6_of(llo[i], lhi[i]) : box6_empty();
+    // subsets with highest leaf 0 or 1 are singletons or the pair {0,1}
+    tab.cost(3) = box6_half_area(box6_join(lb[1], lb[0]));
+    treelet_subset_areas<2>(lb, tab);
+    if (nl > 3) treelet_subset_areas<3>(lb, tab);
+    if (nl > 4) treelet_subset_areas<4>(lb, tab);
+    if (nl > 5) treelet_subset_areas<5>(lb, tab);
+    if (nl > 6) treelet_subset_areas<6>(lb, tab);
   }
-  for (int i = 0; i < nl; i++) copt[1 << i] = lcost[i];
-  for (int sz = 2; sz <= nl; sz++)
-    for (int s = 3; s < S; s++) {
-      if (popc32((uint32_t)s) != sz) continue;
-      float bc = 3.0e38f;
-      int bp = 0;
-      const int delta = (s - 1) & s;  // s without its lowest bit: enumerate each split once
-      int p = (-delta) & s;
-      do {
-        const float c = copt[p] + copt[s ^ p];
-        if (c < bc) { bc = c; bp = p; }
-        p = (p - delta) & s;
-      } while (p != 0);
-      copt[s] = RT_SAH_CT * area[s] + bc;
-      part[s] = (uint8_t)bp;
+  for (int i = 0; i < nl; i++) tab.cost(1 << i) = RT_LDCG(&a.cost[leaves[i]]);
+  // every proper subset of s is numerically smaller than s: ascending order is a valid schedule
+  for (int s = 3; s < S; s++) {
+    if ((s & (s - 1)) == 0) continue;
+    // splits p | s^p with the lowest leaf of s always in s^p: 2^(k-1) - 1 of them for k leaves, i.e. one,
+    // or three plus a multiple of four.  They are read in groups so that the table loads of a group are
+    // in flight together; the first minimum in enumeration order wins, as in a one-by-one scan.
+    const int delta = (s - 1) & s;  // s without its lowest bit
+    int p = (-delta) & s;
+    float bc = tab.cost(p) + tab.cost(s ^ p);
+    int bp = p;
+    p = (p - delta) & s;
+    if (p != 0) {
+      const int p1 = p, p2 = (p1 - delta) & s;
+      const float c1 = tab.cost(p1) + tab.cost(s ^ p1), c2 = tab.cost(p2) + tab.cost(s ^ p2);
+      if (c1 < bc) { bc = c1; bp = p1; }
+      if (c2 < bc) { bc = c2; bp = p2; }
+      p = (p2 - delta) & s;
+      while (p != 0) {
+        const int q0 = p, q1 = (q0 - delta) & s, q2 = (q1 - delta) & s, q3 = (q2 - delta) & s;
+        const float a0 = tab.cost(q0), b0 = tab.cost(s ^ q0), a1 = tab.cost(q1), b1 = tab.cost(s ^ q1);
+        const float a2 = tab.cost(q2), b2 = tab.cost(s ^ q2), a3 = tab.cost(q3), b3 = tab.cost(s ^ q3);
+        const float d0 = a0 + b0, d1 = a1 + b1, d2 = a2 + b2, d3 = a3 + b3;
+        const bool t01 = d1 < d0, t23 = d3 < d2;
+        const float m01 = t01 ? d1 : d0, m23 = t23 ? d3 : d2;
+        const int r01 = t01 ? q1 : q0, r23 = t23 ? q3 : q2;
+        const bool t = m23 < m01;
+        const float m = t ? m23 : m01;
+        const int r = t ? r23 : r01;
+        if (m < bc) { bc = m; bp = r; }
+        p = (q3 - delta) & s;
+      }
     }
-  if (!(copt[S - 1] < cur * 0.9999f)) { a.cost[x] = cur; return; }
+    tab.cost(s) = RT_SAH_CT * tab.cost(s) + bc;
+    tab.part(s) = (uint8_t)bp;
+  }
+  if (!(tab.cost(S - 1) < cur * 0.9999f)) { a.cost[x] = cur; return; }
   // rewrite the treelet: breadth-first over the chosen splits, ids taken from inner[]
   int qs[TREELET_LEAVES], qid[TREELET_LEAVES];
   int qh = 0, qt = 0, next = 1;
@@ -270,7 +307,7 @@ RT_HD void treelet_optimize_node(const BuildArrays& a, int x) {
   while (qh < qt) {
     const int s = qs[qh], id = qid[qh];
     qh++;
-    const int sub[2] = {(int)part[s], s ^ (int)part[s]};
+    const int sub[2] = {(int)tab.part(s), s ^ (int)tab.part(s)};
     int ch[2];
     for (int c = 0; c < 2; c++) {
       if ((sub[c] & (sub[c] - 1)) == 0) {
@@ -294,23 +331,42 @@ RT_HD void treelet_optimize_node(const BuildArrays& a, int x) {
     a.parent[ch[1]] = id;
     a.node_lo[id] = make_float4(lx, ly, lz, u2f(cnt));
     a.node_hi[id] = make_float4(hx, hy, hz, 0.0f);
-    a.cost[id] = copt[s];
+    a.cost[id] = tab.cost(s);
   }
 }
 
 // Round-based driver (GPU): a node is ready when both children are final.  Round 0 = the
 // parents that two leaves reached; every round refines all ready nodes (one thread each, all
 // lanes busy) and queues the parents that became ready.  The tree height bounds the rounds.
-RT_HD void treelet_leaf_arrive(const BuildArrays& a, uint32_t j, uint32_t* queue, uint32_t* qcount) {
+// With `fit` the rounds also do the box fit (the first pass on the GPU): a ready node's box is the
+// union of its two final children, so the separate bottom-up fit with its fence and atomic per
+// level (refit_from_leaf) is not needed.
+RT_HD void treelet_leaf_arrive(const BuildArrays& a, uint32_t j, uint32_t* queue, uint32_t* qcount, bool fit) {
   const int n = (int)a.ntri;
   const int leaf = (n - 1) + (int)j;
+  if (fit) {
+    const uint32_t t = a.vals[j];
+    float4 lo = a.tri_lo[t];
+    lo.w = u2f(1u);
+    a.node_lo[leaf] = lo;
+    a.node_hi[leaf] = a.tri_hi[t];
+  }
   a.cost[leaf] = RT_SAH_CI * half_area(a.node_lo[leaf], a.node_hi[leaf]);
   if (n == 1) return;
   const int p = a.parent[leaf];
   if (RT_ATOMIC_ADD(&a.flags[p], 1u) == 1u) queue[RT_ATOMIC_ADD(qcount, 1u)] = (uint32_t)p;
 }
-RT_HD void treelet_round_node(const BuildArrays& a, uint32_t node, uint32_t* next_queue, uint32_t* next_count) {
-  treelet_optimize_node(a, (int)node);
+template <class Tables>
+RT_HD void treelet_round_node(const BuildArrays& a, uint32_t node, uint32_t* next_queue, uint32_t* next_count, Tables& tab,
+                              bool fit) {
+  if (fit) {
+    const int lc = a.left[node], rc = a.right[node];
+    const float4 l0 = RT_LDCG(&a.node_lo[lc]), l1 = RT_LDCG(&a.node_hi[lc]);
+    const float4 r0 = RT_LDCG(&a.node_lo[rc]), r1 = RT_LDCG(&a.node_hi[rc]);
+    a.node_lo[node] = make_float4(fminf(l0.x, r0.x), fminf(l0.y, r0.y), fminf(l0.z, r0.z), u2f(f2u(l0.w) + f2u(r0.w)));
+    a.node_hi[node] = make_float4(fmaxf(l1.x, r1.x), fmaxf(l1.y, r1.y), fmaxf(l1.z, r1.z), 0.0f);
+  }
+  treelet_optimize_node(a, (int)node, tab);
   if (node == 0u) return;
   const int p = a.parent[node];
   if (RT_ATOMIC_ADD(&a.flags[p], 1u) == 1u) next_queue[RT_ATOMIC_ADD(next_count, 1u)] = (uint32_t)p;
@@ -327,7 +383,8 @@ RT_HD void treelet_from_leaf(const BuildArrays& a, uint32_t j) {
   while (true) {
     RT_FENCE();
     if (RT_ATOMIC_ADD(&a.flags[node], 1u) == 0u) return;
-    treelet_optimize_node(a, node);
+    TreeletLocalTables tab;
+    treelet_optimize_node(a, node, tab);
     if (node == 0) return;
     node = RT_LDCG(&a.parent[node]);
   }

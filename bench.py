@@ -61,6 +61,10 @@ def parse_args():
     ap.add_argument("--accel", type=int, default=0, help="RT_ACCEL_*: 0 = default (binary BVH), 3 = compressed 8-wide BVH")
     ap.add_argument("--flags", type=int, default=0, help="extra rt_scene_desc flags, e.g. 16 = RT_FLAG_NO_REFINE")
     ap.add_argument("--sky", type=int, default=2048, help="procedural skybox face size")
+    ap.add_argument("--e2e", default="host-frame", choices=["host-frame", "copy"],
+                    help="how the frame reaches host memory in the e2e region: host-frame = every rank's k_resolve stores its "
+                         "tiles into one shared pinned host frame (rt_host_frame_*), copy = frame gathered on rank 0's GPU, "
+                         "then one device->host copy")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N > 1: 'peer' = every rank's resolve kernel stores its tiles into rank 0's frame over NVLink "
                          "(falls back to 'nccl' if the frame cannot be shared); 'nccl' = gather collective + de-interleave")
@@ -277,6 +281,47 @@ def main():
     frame_no = {"n": 0}
     stream_handle = torch.cuda.current_stream().cuda_stream
 
+    # ---- end-to-end path: one frame in shared pinned host memory, every rank stores its tiles into it --------------
+    hostf, e2e_mode = None, args.e2e
+    if e2e_mode == "host-frame":
+        names = [f"/rt_b200_frame_{os.getpid()}"] if rank == 0 else [None]
+        if world > 1:
+            dist.broadcast_object_list(names, src=0)
+        ok = torch.ones(1, device=dev)
+        try:
+            if rank == 0:
+                hostf = rt.HostFrame.create(names[0], local_rank, W * H * 4)
+        except rt.RtError as e:
+            sys.stderr.write(f"host frame: {e}\n")
+            ok.zero_()
+        if world > 1:
+            dist.barrier()          # the name exists before anybody opens it
+        try:
+            if rank != 0:
+                hostf = rt.HostFrame.open(names[0], local_rank, W * H * 4)
+        except rt.RtError as e:
+            sys.stderr.write(f"rank {rank} host frame: {e}\n")
+            ok.zero_()
+        if world > 1:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if float(ok.item()) == 0.0:
+            if hostf is not None:
+                hostf.release()
+                hostf = None
+            e2e_mode = "copy"
+    p_host = p_compact.copy()
+    p_host.shard_layout = rt.SHARD_IN_FRAME
+    host_no = {"n": 0}
+
+    def host_step():
+        """one frame straight into the shared host frame: no device frame, no gather, no copy"""
+        host_no["n"] += 1
+        scene.render_into(cam, p_host, hostf.dev_ptr)    # returns when this rank's stores have completed
+        launches["frames"] += 1
+        hostf.signal(rank, host_no["n"])
+        if rank == 0:
+            hostf.wait(world, host_no["n"])
+
     def nccl_step(p, loc, gat, frm):
         scene.render_into(cam, p, loc.data_ptr())
         launches["frames"] += 1
@@ -286,6 +331,8 @@ def main():
             launches["n"] += 1
 
     def step(to_host):
+        if to_host and e2e_mode == "host-frame":
+            return host_step()
         if gather == "peer":
             frame_no["n"] += 1
             scene.render_into(cam, p_dev, peer.ptr)   # this rank's tiles go straight into rank 0's frame
@@ -317,6 +364,17 @@ def main():
             gather_verified = bool(torch.equal(frm, frame))
         del loc, gat, frm
         torch.cuda.empty_cache()
+
+    host_verified = None
+    if e2e_mode == "host-frame":   # once, outside the timed region: the host frame must equal the device frame
+        step(False)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        step(True)
+        if rank == 0:
+            dev_frame = (frame if sharded else local.view(H, W, 4)).cpu().numpy()
+            host_verified = bool((hostf.array(H, W, 4) == dev_frame).all())
 
     def timed(to_host, steps):
         ms, rays = 0.0, 0
@@ -361,6 +419,9 @@ def main():
     scene.set_counting(False)
     fp32 = rt.measure_fp32_tflops(local_rank) if rank == 0 else 0.0
     if rank != 0:
+        if hostf is not None:
+            torch.cuda.synchronize()
+            hostf.release()
         if peer is not None:
             torch.cuda.synchronize()
             peer.release()          # peers unmap before the owner frees
@@ -380,6 +441,9 @@ def main():
         "e2e": {"value": round(e2e_v, 2), "unit": "Mrays/s", "ms_per_step": round(ms_e2e / args.steps, 4),
                 "h2d_bytes_per_step": C.sizeof(rt.CameraVectors) + C.sizeof(rt.FrameParams), "d2h_bytes_per_step": W * H * 4},
         "gpu_launches": int(n_launch), "clocks": clocks,
+        "e2e_path": {"host-frame": "k_resolve of every rank stores its tiles into one frame in shared pinned host memory "
+                                   "(rt_host_frame_*, 128-byte runs over PCIe) + one CPU arrival flag per rank",
+                     "copy": "frame left on rank 0's GPU, then one device->pinned-host copy"}[e2e_mode],
         "stage_ms": {"trace": round(st_last["trace_ms"], 4), "shadow": round(st_last["shadow_ms"], 4),
                      "shade_raygen_resolve": round(st_last["shade_ms"], 4), "frame_in_library": round(st_last["frame_ms"], 4)},
         "bvh": {"nodes": st_last["bvh_nodes"], "bytes": st_last["bvh_bytes"]},
@@ -392,6 +456,8 @@ def main():
         out["gather_mode"] = gather
         if gather_verified is not None:
             out["gather_equals_nccl_path"] = gather_verified
+    if host_verified is not None:
+        out["host_frame_equals_device_frame"] = host_verified
     out["roofline"] = roofline(st_count, st_last["trace_ms"] + st_last["shadow_ms"], st_last["frame_ms"], hbm, hbm_src, fp32,
                                npix_local)
     if world == 1 and not args.no_cpu_baseline:
@@ -400,6 +466,8 @@ def main():
         out["cpu_baseline"] = {"value": round(v, 3), "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample,
                                "ms_per_sample": round(ms, 1)}
     print(json.dumps(out))
+    if hostf is not None:
+        hostf.release()             # the creator also removes the name
     if world > 1:
         dist.barrier()              # the peers have unmapped the frame
         if peer is not None:

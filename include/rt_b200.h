@@ -269,6 +269,23 @@ int rt_peer_frame_wait(int device_id, void* frame, uint64_t frame_bytes, uint32_
 int rt_peer_frame_close(int device_id, void* frame);     /* peer side */
 int rt_peer_frame_destroy(int device_id, void* frame);   /* owner side */
 
+/* Frame in pinned HOST memory that every process of the box stores its tiles into directly: the
+ * end-to-end path of the multi-GPU frame (and of a single GPU), with no device frame and no
+ * device->host copy behind it.  POSIX shared memory `name` (e.g. "/rt_frame_1234") of `bytes` + the
+ * arrival flags, mapped into the calling process and registered with CUDA (portable, mapped).
+ * *dev_out is the device address of the same memory: pass it as rgba_out of rt_render_frame with
+ * output_location = RT_LOCATION_DEVICE and shard_layout = RT_SHARD_IN_FRAME; k_resolve then stores
+ * 128-byte runs of frame rows straight over PCIe, and the pixels are in *host_out when
+ * rt_render_frame has returned.  create = the gathering process (fails if the name exists), open =
+ * everybody else.  rt_host_frame_signal / _wait are the CPU-side arrival flags (store-release after
+ * rt_render_frame / acquire-spin, wrap-safe compare, RT_ERR_CUDA after timeout_ms, 0 = 2000).
+ * close unmaps and unregisters; unlink_name != 0 also removes the name (the creator). */
+int rt_host_frame_create(const char* name, uint64_t bytes, int device_id, void** host_out, void** dev_out);
+int rt_host_frame_open(const char* name, uint64_t bytes, int device_id, void** host_out, void** dev_out);
+int rt_host_frame_signal(void* host, uint64_t bytes, uint32_t rank, uint32_t value);
+int rt_host_frame_wait(void* host, uint64_t bytes, uint32_t n_ranks, uint32_t value, uint32_t timeout_ms);
+int rt_host_frame_close(const char* name, void* host, uint64_t bytes, int device_id, int unlink_name);
+
 /* --- parity / measurement exports --------------------------------------------- */
 /* Primary-ray hit records of a frame: width*height*samples_per_pixel records,
  * index = (y*width + x)*spp + sample.  hits_out is a HOST pointer. */

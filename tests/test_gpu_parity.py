@@ -373,6 +373,48 @@ def test_shards_stored_in_frame_equal_the_full_frame(gpu_rt):
     sc.close()
 
 
+def test_host_frame_receives_the_tiles_of_every_shard(gpu_rt):
+    """rt_host_frame_*: the frame lives in shared pinned host memory, k_resolve stores into it through the
+    mapped device address; a second mapping of the same name (what another rank's process would open) sees
+    the same pixels and flags; whole frame and 3 shards both equal the frame rendered on the device."""
+    import os
+    rt = gpu_rt
+    inputs = scenes.smoke_scene(rt)
+    sc = rt.Scene(inputs, device_id=0)
+    cam = rt.CameraVectors.default()
+    W, H = 200, 136
+    p = rt.FrameParams.make(W, H, 5, 2, tile_w=32, tile_h=16)
+    full = sc.render(cam, p)
+    name = f"/rt_b200_test_{os.getpid()}"
+    hf = rt.HostFrame.create(name, 0, W * H * 4)
+    try:
+        with pytest.raises(rt.RtError):
+            rt.HostFrame.create(name, 0, W * H * 4)       # the name is taken
+        other = rt.HostFrame.open(name, 0, W * H * 4)       # second mapping = another process's view
+        pix = hf.array(H, W, 4)
+        q = p.copy()
+        q.output_location, q.shard_layout = rt.LOCATION_DEVICE, rt.SHARD_IN_FRAME
+        pix[:] = 7
+        sc.render_into(cam, q, hf.dev_ptr)                  # one shard = the whole frame
+        assert np.array_equal(pix, full) and np.array_equal(other.array(H, W, 4), full)
+        pix[:] = 7
+        q.shard_count = 3
+        for s in (2, 0, 1):
+            q.shard_index = s
+            sc.render_into(cam, q, other.dev_ptr if s == 1 else hf.dev_ptr)
+            hf.signal(s, 9) if s != 1 else other.signal(s, 9)
+        hf.wait(3, 9)
+        assert np.array_equal(pix, full)
+        with pytest.raises(rt.RtError):
+            hf.wait(4, 9, timeout_ms=30)
+        other.release()
+    finally:
+        hf.release()
+    with pytest.raises(rt.RtError):
+        rt.HostFrame.open(name, 0, W * H * 4)               # the creator removed the name
+    sc.close()
+
+
 def test_full_size_properties(gpu_rt, ob):
     """BASELINE C3 size (3840x2160, depth 8): size-independent checks — a centred crop rendered by
     the oracle matches the same pixels of the full CUDA frame exactly, and ray counts are consistent."""

@@ -402,6 +402,11 @@ def rt_lib():
         L.rt_peer_frame_wait.argtypes = [C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
         L.rt_peer_frame_close.argtypes = [C.c_int, C.c_void_p]
         L.rt_peer_frame_destroy.argtypes = [C.c_int, C.c_void_p]
+        L.rt_host_frame_create.argtypes = [C.c_char_p, C.c_uint64, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.rt_host_frame_open.argtypes = [C.c_char_p, C.c_uint64, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.rt_host_frame_signal.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32]
+        L.rt_host_frame_wait.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.rt_host_frame_close.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int]
         L.rt_primary_hits.argtypes = [C.c_void_p, C.POINTER(CameraVectors), C.POINTER(FrameParams), C.c_void_p]
         L.rt_trace_rays.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int,
                                     C.c_void_p]
@@ -547,6 +552,46 @@ class PeerFrame:
             L = rt_lib()
             _check((L.rt_peer_frame_destroy if self.owner else L.rt_peer_frame_close)(self.device_id, C.c_void_p(self.ptr)))
             self.ptr = 0
+
+
+class HostFrame:
+    """A frame in shared pinned host memory that every rank's k_resolve stores its tiles into
+    directly (rt_host_frame_*): `.dev_ptr` is the output of Scene.render_into with
+    shard_layout=SHARD_IN_FRAME, `.array(h, w)` the uint8 view of the pixels on the host."""
+
+    def __init__(self, name: str, device_id: int, host_ptr: int, dev_ptr: int, nbytes: int, owner: bool):
+        self.name, self.device_id, self.host_ptr, self.dev_ptr, self.nbytes, self.owner = name, device_id, host_ptr, dev_ptr, nbytes, owner
+
+    @staticmethod
+    def _map(fn, name: str, device_id: int, nbytes: int, owner: bool) -> "HostFrame":
+        h, d = C.c_void_p(), C.c_void_p()
+        _check(fn(name.encode(), nbytes, device_id, C.byref(h), C.byref(d)))
+        return HostFrame(name, device_id, h.value, d.value, nbytes, owner)
+
+    @staticmethod
+    def create(name: str, device_id: int, nbytes: int) -> "HostFrame":
+        return HostFrame._map(rt_lib().rt_host_frame_create, name, device_id, nbytes, True)
+
+    @staticmethod
+    def open(name: str, device_id: int, nbytes: int) -> "HostFrame":
+        return HostFrame._map(rt_lib().rt_host_frame_open, name, device_id, nbytes, False)
+
+    def array(self, *shape) -> np.ndarray:
+        buf = (C.c_uint8 * self.nbytes).from_address(self.host_ptr)
+        a = np.frombuffer(buf, dtype=np.uint8)
+        return a.reshape(shape) if shape else a
+
+    def signal(self, rank: int, value: int):
+        _check(rt_lib().rt_host_frame_signal(C.c_void_p(self.host_ptr), self.nbytes, rank, value & 0xFFFFFFFF))
+
+    def wait(self, n_ranks: int, value: int, timeout_ms: int = 2000):
+        _check(rt_lib().rt_host_frame_wait(C.c_void_p(self.host_ptr), self.nbytes, n_ranks, value & 0xFFFFFFFF, timeout_ms))
+
+    def release(self):
+        if self.host_ptr:
+            _check(rt_lib().rt_host_frame_close(self.name.encode(), C.c_void_p(self.host_ptr), self.nbytes, self.device_id,
+                                                1 if self.owner else 0))
+            self.host_ptr = self.dev_ptr = 0
 
 
 def generate_normals(vertices: np.ndarray, indices: np.ndarray, device_id: int = 0):

@@ -2,6 +2,12 @@
 // argument checking, device memory ownership, instance matrices; all ray tracing happens
 // in the kernels of rt_build.cu / rt_render.cu.  No CPU fallback exists: every compute
 // entry point fails with RT_ERR_NO_DEVICE when no CUDA device is usable.
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#include <cerrno>
+#include <chrono>
 #include <cmath>
 #include <cstring>
 #include <memory>
@@ -481,6 +487,81 @@ int rt_peer_frame_destroy(int device_id, void* frame) {
   if (!frame) return RT_OK;
   RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
   RT_CUDA_TRY(cudaFree(frame), g_err);
+  return RT_OK;
+}
+
+// ---- frame in shared pinned host memory (rt_host_frame_*) ------------------------------------------
+static int host_frame_map(const char* name, uint64_t bytes, int device_id, bool create, void** host_out, void** dev_out) {
+  if (!name || !host_out || !dev_out || bytes == 0) return fail(RT_ERR_INVALID_ARGUMENT, "null argument or empty frame");
+  if (rt_device_count() < 1) return fail(RT_ERR_NO_DEVICE, "no CUDA device");
+  RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
+  const size_t total = peer_flag_offset(bytes) + PEER_FLAG_BYTES;
+  const int fd = shm_open(name, create ? (O_CREAT | O_EXCL | O_RDWR) : O_RDWR, 0600);
+  if (fd < 0) return fail(RT_ERR_INVALID_ARGUMENT, std::string("shm_open ") + name + ": " + std::strerror(errno));
+  if (create && ftruncate(fd, (off_t)total) != 0) {
+    const std::string why = std::strerror(errno);
+    close(fd);
+    shm_unlink(name);
+    return fail(RT_ERR_OUT_OF_MEMORY, "ftruncate: " + why);
+  }
+  void* h = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_POPULATE, fd, 0);
+  close(fd);
+  if (h == MAP_FAILED) {
+    if (create) shm_unlink(name);
+    return fail(RT_ERR_OUT_OF_MEMORY, std::string("mmap: ") + std::strerror(errno));
+  }
+  if (create) std::memset((char*)h + peer_flag_offset(bytes), 0, PEER_FLAG_BYTES);
+  cudaError_t e = cudaHostRegister(h, total, cudaHostRegisterPortable | cudaHostRegisterMapped);
+  void* d = nullptr;
+  if (e == cudaSuccess) e = cudaHostGetDevicePointer(&d, h, 0);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    munmap(h, total);
+    if (create) shm_unlink(name);
+    return fail(RT_ERR_CUDA, std::string("cudaHostRegister: ") + cudaGetErrorString(e));
+  }
+  *host_out = h;
+  *dev_out = d;
+  return RT_OK;
+}
+
+int rt_host_frame_create(const char* name, uint64_t bytes, int device_id, void** host_out, void** dev_out) {
+  return host_frame_map(name, bytes, device_id, true, host_out, dev_out);
+}
+int rt_host_frame_open(const char* name, uint64_t bytes, int device_id, void** host_out, void** dev_out) {
+  return host_frame_map(name, bytes, device_id, false, host_out, dev_out);
+}
+
+int rt_host_frame_signal(void* host, uint64_t bytes, uint32_t rank, uint32_t value) {
+  if (!host || rank >= PEER_FLAG_BYTES / 4) return fail(RT_ERR_INVALID_ARGUMENT, "bad host frame or rank");
+  uint32_t* flags = (uint32_t*)((char*)host + peer_flag_offset(bytes));
+  __atomic_store_n(&flags[rank], value, __ATOMIC_RELEASE);
+  return RT_OK;
+}
+
+int rt_host_frame_wait(void* host, uint64_t bytes, uint32_t n_ranks, uint32_t value, uint32_t timeout_ms) {
+  if (!host || n_ranks == 0 || n_ranks > PEER_FLAG_BYTES / 4) return fail(RT_ERR_INVALID_ARGUMENT, "bad host frame or rank count");
+  const uint32_t* flags = (const uint32_t*)((char*)host + peer_flag_offset(bytes));
+  const auto t0 = std::chrono::steady_clock::now();
+  const auto limit = std::chrono::milliseconds(timeout_ms ? timeout_ms : 2000u);
+  for (uint32_t r = 0; r < n_ranks; r++) {
+    uint32_t spins = 0;
+    while ((int32_t)(__atomic_load_n(&flags[r], __ATOMIC_ACQUIRE) - value) < 0) {
+      if ((++spins & 0xFFFu) == 0 && std::chrono::steady_clock::now() - t0 > limit)
+        return fail(RT_ERR_CUDA, "rt_host_frame_wait: a rank did not deliver its tiles in time");
+    }
+  }
+  return RT_OK;
+}
+
+int rt_host_frame_close(const char* name, void* host, uint64_t bytes, int device_id, int unlink_name) {
+  if (host) {
+    cudaSetDevice(device_id);
+    cudaHostUnregister(host);
+    cudaGetLastError();
+    munmap(host, peer_flag_offset(bytes) + PEER_FLAG_BYTES);
+  }
+  if (unlink_name && name) shm_unlink(name);
   return RT_OK;
 }
 

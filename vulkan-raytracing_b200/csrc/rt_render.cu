@@ -87,7 +87,7 @@ __device__ __forceinline__ uint32_t warp_append(bool pred, uint32_t* counter) {
 __global__ void __launch_bounds__(256) k_raygen(SceneDev scene, FrameUniforms U, uint32_t slot_base, uint32_t nslots,
                                                 float4* __restrict__ rayO, float4* __restrict__ rayD,
                                                 float4* __restrict__ sample, uint32_t* __restrict__ cnt,
-                                                rt_hit* __restrict__ primary) {
+                                                rt_hit* __restrict__ primary, uint32_t* __restrict__ tile_live) {
   const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
   const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const f3 amb = ambient_color();
@@ -129,6 +129,10 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev scene, FrameUniforms U,
         sample[s] = make_float4(0.f, 0.f, 0.f, 0.f);  // padding outside the frame
       }
     }
+    // a tile none of whose rays reaches the scene is final here: k_resolve stores it while the rest is traced
+    // (a warp's 32 slots lie in one tile)
+    if (tile_live && __any_sync(0xFFFFFFFFu, reach) && lane_id() == 0)
+      tile_live[(slot_base + (uint32_t)base) / (U.tile_w * U.tile_h * U.spp)] = 1u;
     const uint32_t dst = warp_append(reach, &cnt[C_NRAY]);
     if (reach) {
       rayO[dst] = make_float4(o.x, o.y, o.z, __uint_as_float(s));
@@ -551,10 +555,14 @@ __global__ void __launch_bounds__(256)
 // by row, so a warp's store is one 128-byte run of a frame row (NVLink moves it as one packet
 // instead of four 32-byte ones); the samples are read through the 8x4 micro-block order they
 // were accumulated in.
-__global__ void __launch_bounds__(256) k_resolve(FrameUniforms U, uint32_t npix, const float4* __restrict__ sample,
-                                                 void* __restrict__ out, uint32_t format) {
+// `part`: 0 = every tile, 1 = only the tiles k_raygen finished (tile_live == 0: stored early, beside the
+// traversal - for a frame in host memory that hides their trip over PCIe), 2 = only the others.
+__global__ void __launch_bounds__(256) k_resolve(FrameUniforms U, uint32_t pix_begin, uint32_t npix, const float4* __restrict__ sample,
+                                                 void* __restrict__ out, uint32_t format,
+                                                 const uint32_t* __restrict__ tile_live, int part) {
   const uint32_t tile_px = U.tile_w * U.tile_h;
-  for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x) {
+  for (uint32_t p = pix_begin + blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x) {
+    if (part != 0 && (tile_live[p / tile_px] != 0u) == (part == 1)) continue;
     uint32_t x, y, pslot = p;
     bool valid;
     size_t dst;
@@ -669,6 +677,12 @@ struct FramePipeline {
     size_t alive_cap = 0;
     cudaEvent_t done = nullptr;
   } sub[RT_MAX_SUB];
+  // early resolve of the tiles k_raygen finished
+  uint32_t* tile_live = nullptr;
+  size_t tile_cap = 0;
+  cudaStream_t early_st[RT_MAX_SUB] = {nullptr, nullptr, nullptr, nullptr};   // highest priority
+  cudaEvent_t ray_done[RT_MAX_SUB] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t early_done[RT_MAX_SUB] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t start = nullptr;
   // what pipeline_frame_stats needs of the last frame (the event arithmetic is done on demand)
   int last_nsub = 0;
@@ -705,6 +719,10 @@ void pipeline_destroy(FramePipeline* p) {
     if (sb.h_alive) cudaFreeHost(sb.h_alive);
   }
   if (p->start) cudaEventDestroy(p->start);
+  cudaFree(p->tile_live);
+  for (auto& e : p->early_st) if (e) cudaStreamDestroy(e);
+  for (auto& e : p->ray_done) if (e) cudaEventDestroy(e);
+  for (auto& e : p->early_done) if (e) cudaEventDestroy(e);
   delete p;
 }
 
@@ -739,6 +757,13 @@ static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std:
     RT_CUDA_TRY(cudaEventCreate(&p->ev[0]), err);
     RT_CUDA_TRY(cudaEventCreate(&p->ev[1]), err);
     RT_CUDA_TRY(cudaEventCreateWithFlags(&p->start, cudaEventDisableTiming), err);
+  }
+  if (!p->early_st[0]) {
+    int least = 0, greatest = 0;
+    RT_CUDA_TRY(cudaDeviceGetStreamPriorityRange(&least, &greatest), err);
+    for (auto& e : p->early_st) RT_CUDA_TRY(cudaStreamCreateWithPriority(&e, cudaStreamNonBlocking, greatest), err);
+    for (auto& e : p->ray_done) RT_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), err);
+    for (auto& e : p->early_done) RT_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), err);
   }
   for (auto& sb : p->sub) {
     if (!sb.aux) {
@@ -868,6 +893,22 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   RT_CUDA_TRY(cudaEventRecord(p->ev[0], st), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->cnt, 0, (size_t)nsub * p->cnt_blocks * C_STRIDE * sizeof(uint32_t), st), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
+  // Tiles whose primary rays all miss the scene (4/5 of C3's) are final after k_raygen: every sub-frame resolves
+  // its own on a high-priority side stream, one block per SM, launched before its first traversal launch so the
+  // blocks are placed first; the stores (PCIe for a frame in host memory) then run beside the traversal.  The
+  // other tiles are resolved at the end.  RT_EARLY_RESOLVE=0: one resolve at the end.
+  static const bool early_env = getenv("RT_EARLY_RESOLVE") ? atoi(getenv("RT_EARLY_RESOLVE")) != 0 : true;
+  const bool early = early_env && rq.d_out != nullptr;
+  if (early) {
+    if (U.n_local_tiles > p->tile_cap) {
+      cudaFree(p->tile_live);
+      p->tile_live = nullptr;
+      p->tile_cap = 0;
+      RT_CUDA_TRY(cudaMalloc(&p->tile_live, (size_t)U.n_local_tiles * sizeof(uint32_t)), err);
+      p->tile_cap = U.n_local_tiles;
+    }
+    RT_CUDA_TRY(cudaMemsetAsync(p->tile_live, 0, (size_t)U.n_local_tiles * sizeof(uint32_t), st), err);
+  }
   if (nsub > 1) {
     RT_CUDA_TRY(cudaEventRecord(p->start, st), err);
     for (int k = 1; k < nsub; k++) RT_CUDA_TRY(cudaStreamWaitEvent(ctx[k].st, p->start, 0), err);
@@ -875,8 +916,17 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   for (int k = 0; k < nsub; k++) {
     SubCtx& c = ctx[k];
     k_raygen<<<stride_blocks(c.nslots, 256), 256, 0, c.st>>>(rq.scene, U, c.slot_base, c.nslots, c.rayO[0], c.rayD[0], p->sample,
-                                                             c.cnt, rq.want_primary ? rq.d_primary : nullptr);
+                                                             c.cnt, rq.want_primary ? rq.d_primary : nullptr,
+                                                             early ? p->tile_live : nullptr);
     launches++;
+    if (early) {
+      RT_CUDA_TRY(cudaEventRecord(p->ray_done[k], c.st), err);
+      RT_CUDA_TRY(cudaStreamWaitEvent(p->early_st[k], p->ray_done[k], 0), err);
+      const uint32_t pix0 = c.slot_base / U.spp, pix1 = (c.slot_base + c.nslots) / U.spp;
+      k_resolve<<<sm_count(), 256, 0, p->early_st[k]>>>(U, pix0, pix1, p->sample, rq.d_out, rq.output_format, p->tile_live, 1);
+      launches++;
+      RT_CUDA_TRY(cudaEventRecord(p->early_done[k], p->early_st[k]), err);
+    }
   }
   // one bounce of one sub-frame, enqueued without waiting for anything
   auto enqueue_bounce = [&](SubCtx& c, uint32_t j) -> int {
@@ -975,8 +1025,11 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     }
   }
   if (rq.d_out) {
-    k_resolve<<<stride_blocks(npix, 256), 256, 0, st>>>(U, (uint32_t)npix, p->sample, rq.d_out, rq.output_format);
+    k_resolve<<<stride_blocks(npix, 256), 256, 0, st>>>(U, 0u, (uint32_t)npix, p->sample, rq.d_out, rq.output_format,
+                                                        p->tile_live, early ? 2 : 0);
     launches++;
+    if (early)
+      for (int k = 0; k < nsub; k++) RT_CUDA_TRY(cudaStreamWaitEvent(st, p->early_done[k], 0), err);
   }
   RT_CUDA_TRY(cudaEventRecord(p->ev[1], st), err);
   RT_CUDA_TRY(cudaGetLastError(), err);

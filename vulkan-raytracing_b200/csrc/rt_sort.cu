@@ -7,8 +7,9 @@
 //   k_os_scan   256-bin exclusive scans -> first output position of every digit, per pass
 //   k_os_pass   per 8-bit digit: each 4096-key tile ranks its keys (stable, warp match_any),
 //               publishes its per-digit counts, finds the counts of all earlier tiles with a
-//               decoupled look-back over the tile status words, and scatters straight to the
-//               final positions: keys and values are read once and written once per pass
+//               decoupled look-back over the tile status words, reorders the tile in shared memory
+//               and writes it out in output order (coalesced runs per digit): keys and values
+//               are read once and written once per pass
 //               (24 B / pair / pass for 64-bit keys; the three-kernel sort it replaces read the
 //               keys twice and needed 3 launches per pass).
 // Tiles are handed out by an atomic counter, so a tile only ever waits for tiles that are
@@ -79,12 +80,14 @@ __device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
 
 // One digit pass.  status: [tile][256] words of this pass, zero on entry; ctrl[0]: tile counter.
 template <class K>
-__global__ void __launch_bounds__(OS_THREADS)
+__global__ void __launch_bounds__(OS_THREADS, 2)
     k_os_pass(const K* __restrict__ kin, const uint32_t* __restrict__ vin, K* __restrict__ kout, uint32_t* __restrict__ vout,
               uint64_t n_host, const uint32_t* __restrict__ count_dev, int shift, const uint32_t* __restrict__ digit_start,
               uint32_t* __restrict__ status, uint32_t* __restrict__ ctrl) {
   __shared__ uint32_t warp_cnt[OS_WARPS][256];
-  __shared__ uint32_t digit_base[256];
+  __shared__ uint32_t digit_base[256];     // global position of the tile's first key of digit d, minus its position in the tile
+  __shared__ uint32_t wsum[OS_WARPS];
+  __shared__ K stage[OS_TILE];             // the tile in output order: keys first, then (same storage) the values
   __shared__ uint32_t s_tile;
   const uint64_t n = count_dev ? (uint64_t)*count_dev : n_host;
   const uint32_t num_tiles = (uint32_t)((n + OS_TILE - 1) / OS_TILE);
@@ -100,7 +103,9 @@ __global__ void __launch_bounds__(OS_THREADS)
     K key[OS_ITEMS];
     uint32_t val[OS_ITEMS];
     uint32_t rank[OS_ITEMS];
-    const uint64_t base = (uint64_t)tile * OS_TILE + (uint64_t)wid * (OS_ITEMS * 32) + lane;
+    const uint64_t tile_base = (uint64_t)tile * OS_TILE;
+    const uint32_t nvalid = (uint32_t)std::min<uint64_t>((uint64_t)OS_TILE, n - tile_base);
+    const uint64_t base = tile_base + (uint64_t)wid * (OS_ITEMS * 32) + lane;
 #pragma unroll
     for (int r = 0; r < OS_ITEMS; r++) {
       const uint64_t p = base + (uint64_t)r * 32;
@@ -122,7 +127,8 @@ __global__ void __launch_bounds__(OS_THREADS)
       rank[r] = prior + before;
     }
     __syncthreads();
-    {  // thread d owns digit d: offsets of the warps inside the tile, then the look-back
+    {  // thread d owns digit d: offsets of the warps inside the tile, position of the digit inside the
+       // tile (block scan), then the look-back
       const uint32_t d = threadIdx.x;
       uint32_t run = 0;
 #pragma unroll
@@ -131,6 +137,13 @@ __global__ void __launch_bounds__(OS_THREADS)
         warp_cnt[w][d] = run;
         run += c;
       }
+      uint32_t x = run;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, o);
+        if (lane >= o) x += y;
+      }
+      if (lane == 31) wsum[wid] = x;
       uint32_t* my = status + (size_t)tile * 256 + d;
       uint32_t excl = 0;
       if (tile == 0) {
@@ -147,18 +160,45 @@ __global__ void __launch_bounds__(OS_THREADS)
         }
         atomicExch(my, OS_FLAG_PREFIX | (excl + run));
       }
-      digit_base[d] = digit_start[d] + excl;
+      __syncthreads();
+      uint32_t in_tile = x - run;   // keys of smaller digits in this tile
+      for (int w = 0; w < wid; w++) in_tile += wsum[w];
+#pragma unroll
+      for (int w = 0; w < OS_WARPS; w++) warp_cnt[w][d] += in_tile;   // now: position in the tile of warp w's first key of digit d
+      digit_base[d] = digit_start[d] + excl - in_tile;
     }
     __syncthreads();
+    // Reorder the tile in shared memory, then write it out in output order: consecutive threads write
+    // consecutive addresses of a digit's run (the direct scatter wrote 32 different runs per warp store).
+    uint32_t pos[OS_ITEMS];
 #pragma unroll
     for (int r = 0; r < OS_ITEMS; r++) {
-      if (base + (uint64_t)r * 32 < n) {
-        const uint32_t d = (uint32_t)(key[r] >> shift) & 0xFFu;
-        const uint32_t dst = digit_base[d] + warp_cnt[wid][d] + rank[r];
-        kout[dst] = key[r];
-        vout[dst] = val[r];
+      const bool valid = base + (uint64_t)r * 32 < n;
+      const uint32_t d = (uint32_t)(key[r] >> shift) & 0xFFu;
+      pos[r] = valid ? warp_cnt[wid][d] + rank[r] : 0xFFFFFFFFu;
+      if (valid) stage[pos[r]] = key[r];
+    }
+    __syncthreads();
+    uint32_t dst[OS_ITEMS];
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; r++) {
+      const uint32_t i = threadIdx.x + (uint32_t)r * OS_THREADS;
+      dst[r] = 0xFFFFFFFFu;
+      if (i < nvalid) {
+        const K k = stage[i];
+        dst[r] = digit_base[(uint32_t)(k >> shift) & 0xFFu] + i;
+        kout[dst[r]] = k;
       }
     }
+    __syncthreads();
+    uint32_t* stage_v = reinterpret_cast<uint32_t*>(stage);
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; r++)
+      if (pos[r] != 0xFFFFFFFFu) stage_v[pos[r]] = val[r];
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < OS_ITEMS; r++)
+      if (dst[r] != 0xFFFFFFFFu) vout[dst[r]] = stage_v[threadIdx.x + (uint32_t)r * OS_THREADS];
     __syncthreads();
   }
 }

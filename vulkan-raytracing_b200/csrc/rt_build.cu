@@ -123,11 +123,16 @@ struct TreeletSmemTables {
   __device__ float& cost(int s) { return c[s * TREELET_THREADS]; }
   __device__ uint8_t& part(int s) { return p[s * TREELET_THREADS]; }
 };
-__global__ void __launch_bounds__(TREELET_THREADS) k_treelet_round(BuildArrays a, const uint32_t* __restrict__ queue, uint32_t count,
+// The round's size is read on the device: the host launches several rounds back to back with a grid sized
+// for the last count it knows (rounds never grow: a node gets ready only after a child of the previous round)
+// and looks at the count once per batch; a round past the root finds 0 and ends at once.
+__global__ void __launch_bounds__(TREELET_THREADS) k_treelet_round(BuildArrays a, const uint32_t* __restrict__ queue,
+                                                                   const uint32_t* __restrict__ count_dev,
                                                                    uint32_t* next_queue, uint32_t* next_count, bool fit) {
   __shared__ float s_cost[(1 << TREELET_LEAVES) * TREELET_THREADS];     // 32 KB
   __shared__ uint8_t s_part[(1 << TREELET_LEAVES) * TREELET_THREADS];   //  8 KB
   TreeletSmemTables tab{s_cost + threadIdx.x, s_part + threadIdx.x};
+  const uint32_t count = *count_dev;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x)
     treelet_round_node(a, queue[i], next_queue, next_count, tab, fit);
 }
@@ -280,15 +285,18 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
         k_treelet_leaves<<<grid_for(N, 256), 256, 0, stream>>>(a, queue[0], qcount, pass == 0);
         mark("treelet leaves");
         int cur = 0;
-        for (int round = 0; round < 4096; round++) {
+        const int batch = dbg ? 1 : 8;   // rounds per look at the count
+        for (int round = 0; round < 4096;) {
           uint32_t count = 0;
           RT_CUDA_TRY(cudaMemcpyAsync(&count, qcount + cur, sizeof count, cudaMemcpyDeviceToHost, stream), err);
           RT_CUDA_TRY(cudaStreamSynchronize(stream), err);
           if (count == 0) break;
-          RT_CUDA_TRY(cudaMemsetAsync(qcount + (cur ^ 1), 0, sizeof(uint32_t), stream), err);
-          k_treelet_round<<<grid_for(count, TREELET_THREADS), TREELET_THREADS, 0, stream>>>(a, queue[cur], count, queue[cur ^ 1], qcount + (cur ^ 1), pass == 0);
-          if (dbg && round < 6) mark("treelet round");
-          cur ^= 1;
+          for (int b = 0; b < batch; b++, round++) {
+            RT_CUDA_TRY(cudaMemsetAsync(qcount + (cur ^ 1), 0, sizeof(uint32_t), stream), err);
+            k_treelet_round<<<grid_for(count, TREELET_THREADS), TREELET_THREADS, 0, stream>>>(a, queue[cur], qcount + cur, queue[cur ^ 1], qcount + (cur ^ 1), pass == 0);
+            if (dbg && round < 6) mark("treelet round");
+            cur ^= 1;
+          }
         }
         mark("treelet rounds (rest)");
       }

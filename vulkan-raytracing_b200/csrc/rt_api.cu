@@ -498,11 +498,15 @@ static int host_frame_map(const char* name, uint64_t bytes, int device_id, bool 
   const size_t total = peer_flag_offset(bytes) + PEER_FLAG_BYTES;
   const int fd = shm_open(name, create ? (O_CREAT | O_EXCL | O_RDWR) : O_RDWR, 0600);
   if (fd < 0) return fail(RT_ERR_INVALID_ARGUMENT, std::string("shm_open ") + name + ": " + std::strerror(errno));
-  if (create && ftruncate(fd, (off_t)total) != 0) {
-    const std::string why = std::strerror(errno);
-    close(fd);
-    shm_unlink(name);
-    return fail(RT_ERR_OUT_OF_MEMORY, "ftruncate: " + why);
+  // posix_fallocate, not ftruncate: a /dev/shm too small for the frame fails here with ENOSPC instead of
+  // with SIGBUS at the first store into a page that cannot be backed
+  if (create) {
+    const int rc = posix_fallocate(fd, 0, (off_t)total);
+    if (rc != 0) {
+      close(fd);
+      shm_unlink(name);
+      return fail(RT_ERR_OUT_OF_MEMORY, std::string("posix_fallocate of the shared frame: ") + std::strerror(rc));
+    }
   }
   void* h = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_POPULATE, fd, 0);
   close(fd);

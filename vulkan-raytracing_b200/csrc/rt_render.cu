@@ -29,7 +29,13 @@
 namespace rt {
 
 enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_NCULL, C_STRIDE = 16 };
-constexpr int TRACE_THREADS = 128;
+// Block size of the persistent traversal kernels.  One warp per CTA: the warps share nothing but the
+// stack array, and a one-warp CTA hands its slot to the next launch the moment its last batch is done
+// (C3 frame 9.08 ms at 128 threads, 9.01 at 64, 8.93 at 32, 9.24 at 256: r01_sweep_occupancy.txt).
+#ifndef RT_TRACE_THREADS
+#define RT_TRACE_THREADS 32
+#endif
+constexpr int TRACE_THREADS = RT_TRACE_THREADS;
 constexpr int STACK_SM = 8;      // stack entries per thread kept in shared memory
 constexpr int STACK_LOCAL = 56;  // overflow entries in local memory
 
@@ -190,10 +196,10 @@ struct TraceSink {
   }
 };
 
-// 8 CTAs x 4 warps per SM (64 registers): the traversal is latency- and issue-bound, and 32
+// 32 resident warps per SM (64 registers): the traversal is latency- and issue-bound, and 32
 // resident warps beat the 20 a 96-register build allows (profiles/r01_sweep_occupancy.txt)
 #ifndef RT_TRACE_MINBLK
-#define RT_TRACE_MINBLK 8
+#define RT_TRACE_MINBLK (1024 / RT_TRACE_THREADS)
 #endif
 #define RT_TRACE_BOUNDS __launch_bounds__(TRACE_THREADS, RT_TRACE_MINBLK)
 template <int ACCEL, bool COUNT>

@@ -7,7 +7,6 @@ rows = [r for r in csv.reader(open(sys.argv[1], errors="replace")) if len(r) > 1
 names = [re.sub(r"\(.*", "", r[4]) for r in rows]
 ns = [float(r[14]) for r in rows]
 first = names.index(next(n for n in names if "k_raygen" in n))
-sub = 2 if "k_raygen" in names[first + 1] else 1   # two sub-frames: their k_raygen launches are adjacent
 agg = collections.OrderedDict()
 for n, t in zip(names[first:], ns[first:]):
     if not n.startswith(("rt::", "void rt::")): continue   # torch fill kernels of bench.py (L2 flush) are not the frame
@@ -20,6 +19,7 @@ for n in list(agg):                                         # the untemplated ke
     if "k_trace" not in n and "k_shadow" not in n:
         c, s = agg[n]; agg[n] = (c * frames / (frames + counting), s * frames / (frames + counting))
 tot = sum(s for _, s in agg.values())
+sub = round(sum("k_raygen" in n for n in names) / (frames + counting))   # one k_raygen per sub-frame
 print(f"{frames} timed-path frames in the list ({sub} sub-frame(s) each); per frame:")
 for n, (c, s) in agg.items():
     print(f"  {n:<28s} x{c / frames:5.1f} {s / frames / 1e6:8.3f} ms {100 * s / tot:5.1f} %")

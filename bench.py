@@ -153,7 +153,7 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix):
+def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix, traffic_applies=True):
     """Algorithmic work of the traversal kernels (k_trace + k_shadow) of one frame, DESIGN.md §5."""
     n_node, n_tri = st_count["nodes_visited"], st_count["tris_tested"]
     n_closest = st_count["rays_primary"] + st_count["rays_secondary"] - st_count.get("rays_top_level", 0)  # rays in the queue
@@ -168,7 +168,7 @@ def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix):
     t_roof = max(frame_bytes / (hbm_gbs * 1e9), frame_flops / (fp32_tflops * 1e12) if fp32_tflops else 0.0)
     path = os.path.join(ROOT, "profiles", "traffic.json")
     traffic = None
-    if os.path.exists(path):
+    if traffic_applies and os.path.exists(path):   # the ncu capture is of the N=1 C3 frame; null for any other workload
         try:
             traffic = json.load(open(path)).get("k_trace_dram_bytes_per_frame")
         except Exception:
@@ -177,6 +177,8 @@ def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix):
         "bound": "hbm", "kernel": "k_trace+k_shadow (all traversal launches of one frame)",
         "achieved": round(achieved, 1), "peak": hbm_gbs, "peak_source": hbm_src, "unit": "GB/s",
         "frac": round(achieved / hbm_gbs, 4), "traffic": traffic,
+        "note": "achieved = algorithmic node + triangle + ray-state bytes / traversal time, cache hits not discounted (SURVEY 8d); "
+                "frac > 1 means the working set is served from L1/L2 - `traffic` is what DRAM moved (ncu), see DESIGN.md 5.3",
         "algorithmic_bytes_per_frame": int(trav_bytes), "traversal_ms": round(trav_ms, 4),
         "nodes_visited": int(n_node), "tris_tested": int(n_tri), "node_bytes": node_b, "tri_bytes": tri_b, "boxes_per_node": children,
         "flop_term": {"flops_per_frame": int(trav_flops), "achieved_tflops": round(trav_flops / (trav_ms * 1e-3) / 1e12, 3),
@@ -459,7 +461,7 @@ def main():
     if host_verified is not None:
         out["host_frame_equals_device_frame"] = host_verified
     out["roofline"] = roofline(st_count, st_last["trace_ms"] + st_last["shadow_ms"], st_last["frame_ms"], hbm, hbm_src, fp32,
-                               npix_local)
+                               npix_local, traffic_applies=(wl == "c3" and world == 1 and args.accel in (0, 1)))
     if world == 1 and not args.no_cpu_baseline:
         p_cpu = rt.FrameParams.make(W, H, depth, spp)
         v, ms, cores, sample = cpu_arm(rt, inputs, cam, p_cpu, 1, 0)

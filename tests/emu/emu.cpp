@@ -215,6 +215,50 @@ int emu_scene_set_materials(void* s, const rt_material* m, uint32_t n) {
   memcpy(es->mat.data(), m, n * sizeof(MaterialDev));
   return 0;
 }
+// One treelet on its own (tests/test_emu.py::test_treelet_dp_finds_the_optimum): n <= 7 leaf boxes
+// (6 floats each) and leaf costs hang off a right-leaning chain of n - 1 inner nodes; the root's
+// treelet is optimised with the device code.  Returns the SAH cost of the chain in *cost_before,
+// of the result in *cost_after, and the rewritten left/right child ids (inner i = i, leaf j = n-1+j).
+int emu_treelet(uint32_t n, const float* boxes, const float* leaf_cost, float* cost_before, float* cost_after,
+                int32_t* left_out, int32_t* right_out) {
+  if (n < 2 || n > (uint32_t)TREELET_LEAVES) return 1;
+  std::vector<float4> node_lo(2 * n), node_hi(2 * n);
+  std::vector<int32_t> parent(2 * n), left(n), right(n);
+  std::vector<float> cost(2 * n);
+  BuildArrays a{};
+  a.ntri = n;
+  a.parent = parent.data(); a.left = left.data(); a.right = right.data();
+  a.node_lo = node_lo.data(); a.node_hi = node_hi.data(); a.cost = cost.data();
+  const int L = (int)n - 1;
+  for (uint32_t j = 0; j < n; j++) {
+    const float* b = boxes + 6 * j;
+    node_lo[L + j] = make_float4(b[0], b[1], b[2], u2f(1u));
+    node_hi[L + j] = make_float4(b[3], b[4], b[5], 0.0f);
+    cost[L + j] = leaf_cost[j];
+  }
+  for (int i = 0; i < L; i++) {
+    left[i] = L + i;
+    right[i] = i + 1 < L ? i + 1 : L + (int)n - 1;
+    parent[left[i]] = i;
+    parent[right[i]] = i;
+  }
+  parent[0] = -1;
+  float before = 0.0f;
+  for (int i = L - 1; i >= 0; i--) {
+    const float4 l0 = node_lo[left[i]], l1 = node_hi[left[i]], r0 = node_lo[right[i]], r1 = node_hi[right[i]];
+    node_lo[i] = make_float4(fminf(l0.x, r0.x), fminf(l0.y, r0.y), fminf(l0.z, r0.z), u2f(f2u(l0.w) + f2u(r0.w)));
+    node_hi[i] = make_float4(fmaxf(l1.x, r1.x), fmaxf(l1.y, r1.y), fmaxf(l1.z, r1.z), 0.0f);
+    before += RT_SAH_CT * half_area(node_lo[i], node_hi[i]);
+  }
+  for (uint32_t j = 0; j < n; j++) before += leaf_cost[j];
+  TreeletLocalTables tab;
+  treelet_optimize_node(a, 0, tab);
+  *cost_before = before;
+  *cost_after = cost[0];
+  for (int i = 0; i < L; i++) { left_out[i] = left[i]; right_out[i] = right[i]; }
+  return 0;
+}
+
 uint64_t emu_bvh_nodes(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].nodes; }
 const void* emu_wide_nodes(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].wide.data(); }
 const void* emu_bvh2_nodes(void* s, uint32_t mesh) { return ((EmuScene*)s)->blas[mesh].bvh2.data(); }

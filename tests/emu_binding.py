@@ -27,6 +27,8 @@ def lib():
         L.emu_bvh2_nodes.argtypes = [C.c_void_p, C.c_uint32]
         L.emu_leaf_tris.restype = C.c_void_p
         L.emu_leaf_tris.argtypes = [C.c_void_p, C.c_uint32]
+        L.emu_treelet.argtypes = [C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float),
+                                  C.c_void_p, C.c_void_p]
         L.emu_slot_to_pixel.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         _lib = L
     return _lib
@@ -93,3 +95,16 @@ def slot_to_pixel(params, pslot):
     x, y = C.c_uint32(), C.c_uint32()
     ok = lib().emu_slot_to_pixel(C.byref(params), pslot, C.byref(x), C.byref(y))
     return bool(ok), x.value, y.value
+
+
+def treelet(boxes, leaf_cost):
+    """Device treelet optimisation of one root over n <= 7 leaves (emu_treelet): returns
+    (cost of the initial chain, cost after, left[n-1], right[n-1])."""
+    b = np.ascontiguousarray(boxes, np.float32).reshape(-1, 6)
+    c = np.ascontiguousarray(leaf_cost, np.float32)
+    n = b.shape[0]
+    before, after = C.c_float(), C.c_float()
+    left, right = np.zeros(n - 1, np.int32), np.zeros(n - 1, np.int32)
+    assert lib().emu_treelet(n, b.ctypes.data, c.ctypes.data, C.byref(before), C.byref(after), left.ctypes.data,
+                             right.ctypes.data) == 0
+    return before.value, after.value, left, right

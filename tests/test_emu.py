@@ -210,6 +210,71 @@ def test_binary_bvh_structure(rt, emu, passes, monkeypatch):
 test_binary_bvh_structure.area = {}
 
 
+def test_treelet_dp_finds_the_optimum(emu):
+    """The treelet optimiser (dynamic programme over leaf subsets, splits read in groups of one, three and
+    four) against an exhaustive search in double precision: for 2..7 random leaf boxes the cost it reports is
+    the minimum over all binary topologies (or the unchanged chain when the gain is below 0.01 %), and the
+    tree it writes is a tree over exactly those leaves with that cost."""
+    from functools import lru_cache
+    rng = np.random.default_rng(5)
+    CT, CI = 1.0, 1.3
+
+    def half_area(lo, hi):
+        d = hi - lo
+        return float(d[0] * d[1] + d[1] * d[2] + d[2] * d[0])
+
+    for trial in range(60):
+        n = 2 + trial % 6
+        lo = rng.uniform(-4, 4, (n, 3))
+        hi = lo + rng.uniform(0.01, 2.5, (n, 3)) * rng.choice([0.2, 1.0, 3.0])
+        boxes = np.concatenate([lo, hi], 1).astype(np.float32)
+        lo, hi = boxes[:, :3].astype(np.float64), boxes[:, 3:].astype(np.float64)
+        # leaf costs: single triangles (CI * area) or whole subtrees (larger)
+        lcost = np.array([CI * half_area(lo[j], hi[j]) * rng.choice([1.0, 1.0, 4.0]) for j in range(n)], np.float32)
+
+        def area(mask):
+            idx = [j for j in range(n) if mask >> j & 1]
+            return half_area(lo[idx].min(0), hi[idx].max(0))
+
+        @lru_cache(None)
+        def best(mask):
+            if mask & (mask - 1) == 0:
+                return float(lcost[mask.bit_length() - 1])
+            sub, m = (mask - 1) & mask, float("inf")
+            while sub:
+                if sub < (mask ^ sub):          # each unordered split once
+                    m = min(m, best(sub) + best(mask ^ sub))
+                sub = (sub - 1) & mask
+            return CT * area(mask) + m
+
+        before, after, left, right = emu.treelet(boxes, lcost)
+        opt = best((1 << n) - 1)
+        chain = sum(CT * area(((1 << n) - 1) & ~((1 << i) - 1)) for i in range(n - 1)) + float(lcost.sum())
+        assert before == pytest.approx(chain, rel=1e-5)
+        assert opt <= chain * (1 + 1e-7)
+        if opt < 0.9998 * chain:
+            assert after == pytest.approx(opt, rel=2e-5), (n, trial)
+        elif opt > 0.99995 * chain:
+            assert after == pytest.approx(chain, rel=2e-5)
+        else:
+            assert opt * (1 - 2e-5) <= after <= chain * (1 + 2e-5)
+        # the tree that was written: every leaf once, its SAH cost is the reported one
+        L = n - 1
+        seen = []
+
+        def walk(node):
+            if node >= L:
+                seen.append(node - L)
+                return 1 << (node - L), float(lcost[node - L])
+            ml, cl = walk(int(left[node]))
+            mr, cr = walk(int(right[node]))
+            return ml | mr, CT * area(ml | mr) + cl + cr
+
+        mask, cost = walk(0)
+        assert sorted(seen) == list(range(n)) and mask == (1 << n) - 1
+        assert cost == pytest.approx(after, rel=2e-5)
+
+
 def test_trace_rays_matches_oracle_brute_force(rt, ob, emu):
     inputs = scenes.c3_scene(rt, level=3, sky_size=8)
     rng = np.random.default_rng(11)

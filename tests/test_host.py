@@ -55,6 +55,32 @@ def test_no_device_means_error_not_fallback(rt):
         rt.sort_pairs(np.arange(4, dtype=np.uint64), np.arange(4, dtype=np.uint32))
 
 
+def test_host_frame_without_a_device_and_its_arrival_flags(rt):
+    """rt_host_frame_create needs a CUDA device (the frame is registered with it) and leaves no shared-memory
+    name behind when there is none; the arrival flags behind the frame are plain host code: ranks report a
+    frame number, the wait returns once all have reached it (older numbers count as reached) and fails after
+    its timeout when one is missing."""
+    name = f"/rt_b200_cpu_test_{os.getpid()}"
+    if rt.device_count() == 0:
+        with pytest.raises(rt.RtError, match="no CUDA device"):
+            rt.HostFrame.create(name, 0, 4096)
+        assert not os.path.exists("/dev/shm" + name)
+    nbytes = 1000                                         # the flags start at the next 256-byte boundary
+    buf = np.zeros(1024 + 4096, np.uint8)
+    hf = rt.HostFrame(name, 0, buf.ctypes.data, 0, nbytes, False)
+    for r in (2, 0, 1):
+        hf.signal(r, 7)
+    hf.wait(3, 7)
+    hf.wait(3, 6)
+    with pytest.raises(rt.RtError, match="did not deliver"):
+        hf.wait(4, 7, timeout_ms=20)
+    flags = buf[1024:1024 + 16].view(np.uint32)
+    assert flags.tolist() == [7, 7, 7, 0] and not buf[:1024].any()
+    with pytest.raises(rt.RtError):
+        hf.signal(5000, 1)                                # more ranks than flags
+    hf.host_ptr = 0                                       # nothing to unmap: the buffer is numpy's
+
+
 @pytest.mark.skipif(not os.path.isdir(REF), reason="reference checkout absent")
 @pytest.mark.parametrize("name", ["cube", "teapot"])
 def test_loader_reproduces_reference_packing(rt, name):

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RT_B200_ABI_VERSION 1u
+#define RT_B200_ABI_VERSION 2u
 
 typedef enum rt_status {
   RT_OK = 0,
@@ -174,9 +174,14 @@ typedef struct rt_stats {
   uint32_t node_bytes;        /* bytes per node of the active layout */
   uint32_t tri_bytes;         /* bytes per leaf triangle of the active layout */
   uint32_t ray_state_bytes;   /* bytes of ray state written then read per ray */
-  uint32_t reserved;
+  uint32_t max_tree_depth;    /* deepest BLAS of the scene (levels of binary nodes above a leaf); rt_scene_build
+                                 refuses a mesh deeper than the traversal stacks (RT_ERR_UNSUPPORTED) */
   uint64_t rays_top_level;    /* of rays_primary: traces answered by the scene's top level (no
                                  instance box reached), which never enter the ray queue */
+  uint32_t stack_overflow;    /* != 0: a traversal stack entry was dropped during the last frame / ray batch
+                                 (geometry may be missing from the result); cannot happen for a scene the
+                                 build accepted, reported so that it can never be silent */
+  uint32_t reserved;
 } rt_stats;
 
 /* --- library ---------------------------------------------------------------- */

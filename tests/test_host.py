@@ -28,7 +28,7 @@ def test_rt_b200_exports_every_declared_symbol(rt):
     for n in names:
         assert hasattr(lib, n), f"librt_b200.so does not export {n}"
     lib.rt_abi_version.restype = C.c_uint32
-    assert lib.rt_abi_version() == 1
+    assert lib.rt_abi_version() == 2
     assert lib.rt_device_count() >= 0
 
 

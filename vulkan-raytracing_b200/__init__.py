@@ -145,7 +145,8 @@ class Stats(C.Structure):
                 ("n_miss", C.c_uint64), ("n_hit", C.c_uint64), ("nodes_visited", C.c_uint64),
                 ("tris_tested", C.c_uint64), ("kernel_launches", C.c_uint64), ("bvh_nodes", C.c_uint64),
                 ("bvh_bytes", C.c_uint64), ("node_bytes", C.c_uint32), ("tri_bytes", C.c_uint32),
-                ("ray_state_bytes", C.c_uint32), ("reserved", C.c_uint32), ("rays_top_level", C.c_uint64)]
+                ("ray_state_bytes", C.c_uint32), ("max_tree_depth", C.c_uint32), ("rays_top_level", C.c_uint64),
+                ("stack_overflow", C.c_uint32), ("reserved", C.c_uint32)]
 
     def as_dict(self) -> dict:
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}

@@ -246,6 +246,7 @@ int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
     hb[i] = s->blas[i].dev;
     s->stats.bvh_nodes += s->blas[i].node_count;
     s->stats.bvh_bytes += s->blas[i].bytes;
+    s->stats.max_tree_depth = std::max(s->stats.max_tree_depth, s->blas[i].depth);
   }
   s->stats.node_bytes = accel == ACCEL_WIDE ? 80 : (accel == ACCEL_BVH2 ? 64 : 0);
   s->stats.tri_bytes = 48;

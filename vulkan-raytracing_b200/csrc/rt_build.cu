@@ -31,6 +31,7 @@ int sm_count() {
 __global__ void k_init_bounds(uint32_t* bounds) {
   const int i = threadIdx.x;
   if (i < 12) bounds[i] = ((i % 6) < 3) ? 0xFFFFFFFFu : 0u;
+  if (i >= 12 && i < 16) bounds[i] = 0u;   // [12] = depth of the final tree (k_tree_depth)
 }
 
 __device__ __forceinline__ float warp_min(float v) {
@@ -147,6 +148,16 @@ __global__ void __launch_bounds__(256) k_emit_bvh2(BuildArrays a, float4* nodes,
     if (i + 1 < a.ntri) emit_bvh2_node(a, (int)i, nodes);
     emit_tri(a, i, a.vals[i], tris);
   }
+}
+
+// depth of the final binary tree -> bounds[12] (one parent walk per leaf, warp-reduced)
+__global__ void __launch_bounds__(256) k_tree_depth(BuildArrays a) {
+  uint32_t d = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.ntri; i += gridDim.x * blockDim.x)
+    d = max(d, tree_depth_of_leaf(a, i));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) d = max(d, __shfl_xor_sync(0xFFFFFFFFu, d, o));
+  if ((threadIdx.x & 31) == 0 && d) atomicMax(&a.bounds[12], d);
 }
 
 __global__ void __launch_bounds__(256) k_emit_brute(BuildArrays a, float4* tris) {
@@ -302,6 +313,10 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
       }
     }
   }
+  if (accel != ACCEL_BRUTE && ntri > 1) {
+    k_tree_depth<<<grid_for(N, 256), 256, 0, stream>>>(a);
+    mark("tree depth");
+  }
   RT_CUDA_TRY(cudaGetLastError(), err);
 
   if (accel == ACCEL_WIDE) {
@@ -334,7 +349,7 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
     k_emit_brute<<<grid_for(N, 256), 256, 0, stream>>>(a, (float4*)b.d_tris);
     b.bytes = N * 48;
   }
-  uint32_t hb[12];
+  uint32_t hb[13];
   RT_CUDA_TRY(cudaEventRecord(ev1, stream), err);
   RT_CUDA_TRY(cudaMemcpyAsync(hb, a.bounds, sizeof hb, cudaMemcpyDeviceToHost, stream), err);
   RT_CUDA_TRY(cudaStreamSynchronize(stream), err);
@@ -363,6 +378,18 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
   b.dev.nodes = (const float4*)b.d_nodes;
   b.dev.tris = (const float4*)b.d_tris;
   b.dev.nnodes = (uint32_t)b.node_count;
+  // The traversal stacks hold RT_MAX_TREE_DEPTH entries (binary) / one node group + one postponed
+  // triangle group per level (8-wide, hence half): a deeper tree is refused here, at build time,
+  // instead of dropping stack entries at render time.  RT_DEPTH_LIMIT lowers the limit (tests).
+  b.depth = hb[12];
+  static const uint32_t depth_env = getenv("RT_DEPTH_LIMIT") ? (uint32_t)atoi(getenv("RT_DEPTH_LIMIT")) : 0u;
+  uint32_t limit = accel == ACCEL_WIDE ? RT_MAX_TREE_DEPTH / 2 : RT_MAX_TREE_DEPTH;
+  if (depth_env) limit = std::min(limit, depth_env);
+  if (accel != ACCEL_BRUTE && b.depth > limit) {
+    err = "mesh not supported: its acceleration structure is " + std::to_string(b.depth) + " levels deep, the traversal stack holds " +
+          std::to_string(limit);
+    return RT_ERR_UNSUPPORTED;
+  }
   return RT_OK;
 }
 

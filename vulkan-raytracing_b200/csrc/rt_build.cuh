@@ -543,6 +543,22 @@ RT_HD void collapse_node(const BuildArrays& a, uint32_t w) {
   o[4] = make_uint4(qhy[0], qhy[1], qhz[0], qhz[1]);
 }
 
+// Number of binary nodes above leaf j (sorted position) in the final tree: the stack an ordered
+// traversal needs on the way to that leaf is at most this.  Walks the parent links (valid after
+// the treelet pass, which rewrites them with the children).  The bound on the walk only guards
+// against a corrupt tree.
+RT_HD uint32_t tree_depth_of_leaf(const BuildArrays& a, uint32_t j) {
+  const int n = (int)a.ntri;
+  int node = a.parent[(n - 1) + (int)j];
+  uint32_t d = 0;
+  while (node >= 0 && d < 100000u) {
+    d++;
+    if (node == 0) break;
+    node = a.parent[node];
+  }
+  return d;
+}
+
 // Binary-tree cross-check layout (ACCEL_BVH2): node i -> 4 x float4, leaves = sorted slots
 RT_HD void emit_bvh2_node(const BuildArrays& a, int i, float4* out) {
   const int n = (int)a.ntri;

@@ -28,6 +28,7 @@ struct BlasHost {
   void* d_nodes = nullptr;
   void* d_tris = nullptr;
   uint64_t node_count = 0, bytes = 0;
+  uint32_t depth = 0;                          // levels of binary nodes above the deepest leaf
 };
 
 // Builds the acceleration structure of one mesh already resident on the device.

@@ -22,13 +22,25 @@
 #include <cstdlib>
 #include <cstring>
 
+// Traversal stacks are sized for the deepest tree build_blas accepts (RT_MAX_TREE_DEPTH); should an
+// entry ever not fit it is dropped *safely* (the stack pointer does not move) and this device word
+// records it, so a frame with missing geometry cannot pass silently: rt_get_stats reports it.
+#include <cuda_runtime.h>
+#include <cstdint>
+namespace rt { __device__ uint32_t g_trav_flags; }
+#if defined(__CUDA_ARCH__)
+#define RT_FLAG_OVERFLOW() atomicOr(&::rt::g_trav_flags, 1u)
+#else
+#define RT_FLAG_OVERFLOW() ((void)0)   // host pass of the RT_HD functions: never executed
+#endif
+
 #include "rt_internal.h"
 #include "rt_persist.cuh"
 #include "rt_wave.cuh"
 
 namespace rt {
 
-enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_NCULL, C_STRIDE = 16 };
+enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_NCULL, C_NSEC, C_STRIDE = 16 };
 // Block size of the persistent traversal kernels.  One warp per CTA: the warps share nothing but the
 // stack array, and a one-warp CTA hands its slot to the next launch the moment its last batch is done
 // (C3 frame 9.08 ms at 128 threads, 9.01 at 64, 8.93 at 32, 9.24 at 256: r01_sweep_occupancy.txt).
@@ -37,7 +49,7 @@ enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_
 #endif
 constexpr int TRACE_THREADS = RT_TRACE_THREADS;
 constexpr int STACK_SM = 8;      // stack entries per thread kept in shared memory
-constexpr int STACK_LOCAL = 56;  // overflow entries in local memory
+constexpr int STACK_LOCAL = RT_MAX_TREE_DEPTH - STACK_SM;  // overflow entries in local memory
 
 // Traversal stack: the first STACK_SM entries live in shared memory (column per thread,
 // bank-conflict free), the rarely used rest in local memory.
@@ -52,6 +64,7 @@ struct HybridStack {
   __device__ __forceinline__ void push(uint2 v) {
     if (sp < STACK_SM) sm[sp * TRACE_THREADS] = v;
     else if (sp < STACK_SM + STACK_LOCAL) loc[sp - STACK_SM] = v;
+    else { RT_FLAG_OVERFLOW(); return; }   // dropped, flagged; pop() stays in bounds
     sp++;
   }
   __device__ __forceinline__ uint2 pop() {
@@ -396,6 +409,10 @@ __global__ void RT_TRACE_BOUNDS
   }
 }
 
+}  // namespace rt
+#include "rt_path.cuh"   // the bounce-fused path kernel (uses lit_color, warp helpers, the counter slots)
+namespace rt {
+
 // ---- warp-synchronous variants (rt_wave.cuh) ---------------------------------------------------
 struct WaveTraceSource {
   const float4* rayO;
@@ -696,6 +713,7 @@ struct FramePipeline {
   uint64_t last_launches = 0;
   std::vector<uint32_t> h_all;
   unsigned long long h64[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  uint32_t h_flags = 0;          // g_trav_flags of the last frame / ray batch
   bool stats_pending = false;
 };
 
@@ -874,6 +892,13 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   static const uint64_t sub_min_slots = getenv("RT_SUBFRAMES_MIN") ? strtoull(getenv("RT_SUBFRAMES_MIN"), nullptr, 10) : (12ull << 20);
   const bool may_sort = accel != ACCEL_BRUTE && sort_from <= (int)U.max_bounce && sort_from <= sort_to;
   const bool wave = accel == ACCEL_WIDE && wave_on && rq.scene.tlas == nullptr;
+  // The bounce-fused path kernel (rt_path.cuh): binary BVH, instances looped (no top-level tree).
+  // RT_FUSED=0 selects the per-bounce wavefront launches for the same frame.
+  static const bool fused_env = getenv("RT_FUSED") ? atoi(getenv("RT_FUSED")) != 0 : true;
+  static const int path_serve = getenv("RT_PATH_SERVE") ? atoi(getenv("RT_PATH_SERVE")) : 12;
+  static const int path_leaf = getenv("RT_PATH_LEAF") ? atoi(getenv("RT_PATH_LEAF")) : 12;
+  static const int path_chunk = getenv("RT_PATH_CHUNK") ? atoi(getenv("RT_PATH_CHUNK")) : 64;
+  const bool fused = fused_env && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && !may_sort && rq.scene.n_inst <= 32u;
   const int nsub = (sub_env >= 2 && nslots >= sub_min_slots && !may_sort && !wave)
                        ? (int)std::min<uint32_t>((uint32_t)std::min(sub_env, RT_MAX_SUB), U.n_local_tiles) : 1;
 
@@ -899,6 +924,11 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   RT_CUDA_TRY(cudaEventRecord(p->ev[0], st), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->cnt, 0, (size_t)nsub * p->cnt_blocks * C_STRIDE * sizeof(uint32_t), st), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
+  {
+    void* fl = nullptr;
+    RT_CUDA_TRY(cudaGetSymbolAddress(&fl, g_trav_flags), err);
+    RT_CUDA_TRY(cudaMemsetAsync(fl, 0, sizeof(uint32_t), st), err);
+  }
   // Tiles whose primary rays all miss the scene (4/5 of C3's) are final after k_raygen: every sub-frame resolves
   // its own on a high-priority side stream, one block per SM, launched before its first traversal launch so the
   // blocks are placed first; the stores (PCIe for a frame in host memory) then run beside the traversal.  The
@@ -1011,6 +1041,37 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     }
     return RT_OK;
   };
+  // the whole bounce loop of one sub-frame in one persistent launch
+  auto enqueue_path = [&](SubCtx& c) -> int {
+    FramePipeline::Sub& sb = *c.sb;
+    PathArgs pa;
+    pa.cnt = c.cnt;
+    pa.rayO = c.rayO[0];
+    pa.rayD = c.rayD[0];
+    pa.sample = p->sample;
+    pa.primary = rq.want_primary ? rq.d_primary : nullptr;
+    pa.stats64 = p->stats64;
+    pa.t_serve = std::max(1, std::min(32, path_serve));
+    pa.t_leaf = std::max(1, std::min(32, path_leaf));
+    pa.chunk = std::max(32, path_chunk) & ~31;
+    static int blocks[2] = {0, 0};
+    if (!blocks[0]) { blocks[0] = persistent_blocks(k_path<false>, 32); blocks[1] = persistent_blocks(k_path<true>, 32); }
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[0], c.st), err);
+    if (counting) k_path<true><<<blocks[1], 32, 0, c.st>>>(rq.scene, U, pa);
+    else k_path<false><<<blocks[0], 32, 0, c.st>>>(rq.scene, U, pa);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[1], c.st), err);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[2], c.st), err);   // no separate shadow launches: empty interval
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[3], c.st), err);
+    launches++;
+    c.last_bounce = 0;
+    return RT_OK;
+  };
+  if (fused) {
+    for (int k = 0; k < nsub; k++) {
+      rc = enqueue_path(ctx[k]);
+      if (rc != RT_OK) return rc;
+    }
+  } else
   for (uint32_t j = 0; j <= U.max_bounce; j++) {
     bool any = false;
     for (int k = 0; k < nsub; k++) {
@@ -1024,7 +1085,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   // join: every sub-frame's shadow rays, then sub-frame 1 into the caller's stream
   for (int k = nsub - 1; k >= 0; k--) {
     SubCtx& c = ctx[k];
-    if (shadow_async) RT_CUDA_TRY(cudaStreamWaitEvent(c.st, c.sb->sev[2 * c.last_bounce + 1], 0), err);
+    if (shadow_async && !fused) RT_CUDA_TRY(cudaStreamWaitEvent(c.st, c.sb->sev[2 * c.last_bounce + 1], 0), err);
     if (k > 0) {
       RT_CUDA_TRY(cudaEventRecord(c.sb->done, c.st), err);
       RT_CUDA_TRY(cudaStreamWaitEvent(st, c.sb->done, 0), err);
@@ -1045,7 +1106,9 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   p->h_all.resize((size_t)nsub * cnt_words);
   RT_CUDA_TRY(cudaMemcpyAsync(p->h_all.data(), p->cnt, p->h_all.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), err);
   RT_CUDA_TRY(cudaMemcpyAsync(p->h64, p->stats64, sizeof p->h64, cudaMemcpyDeviceToHost, st), err);
+  RT_CUDA_TRY(cudaMemcpyFromSymbolAsync(&p->h_flags, g_trav_flags, sizeof(uint32_t), 0, cudaMemcpyDeviceToHost, st), err);
   RT_CUDA_TRY(cudaStreamSynchronize(st), err);
+  if (stats) stats->stack_overflow = p->h_flags & 1u;
   p->last_nsub = nsub;
   for (int k = 0; k < nsub; k++) p->last_bounce[k] = ctx[k].last_bounce;
   p->last_launches = launches;
@@ -1116,6 +1179,7 @@ void pipeline_frame_stats(FramePipeline* p, rt_stats* stats) {
     for (uint32_t j = 0; j <= last_bounce; j++) {
       const uint32_t* c = &p->h_cnt[(size_t)j * C_STRIDE];
       if (j > 0) stats->rays_secondary += c[C_NRAY];
+      stats->rays_secondary += c[C_NSEC];   // the fused path kernel counts all bounces >= 1 here
       stats->rays_shadow += c[C_NSHADOW];
       stats->n_miss += c[C_NMISS];
       stats->n_hit += (uint64_t)c[C_NDIFF] + c[C_NSPEC];
@@ -1134,6 +1198,11 @@ int pipeline_trace_batch(FramePipeline* p, const SceneDev& scene, uint64_t n, co
   p->stats_pending = false;   // the stats below replace those of the last frame
   if (!p->stats64) RT_CUDA_TRY(cudaMalloc(&p->stats64, 8 * sizeof(unsigned long long)), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
+  {
+    void* fl = nullptr;
+    RT_CUDA_TRY(cudaGetSymbolAddress(&fl, g_trav_flags), err);
+    RT_CUDA_TRY(cudaMemsetAsync(fl, 0, sizeof(uint32_t), st), err);
+  }
   const int blocks = (int)std::max<uint64_t>(1, std::min<uint64_t>((n + TRACE_THREADS - 1) / TRACE_THREADS, (uint64_t)sm_count() * 8));
 #define CALL_BATCH(A, C)                                                                                             \
   {                                                                                                                  \
@@ -1145,8 +1214,10 @@ int pipeline_trace_batch(FramePipeline* p, const SceneDev& scene, uint64_t n, co
   RT_CUDA_TRY(cudaGetLastError(), err);
   unsigned long long h64[8];
   RT_CUDA_TRY(cudaMemcpyAsync(h64, p->stats64, sizeof h64, cudaMemcpyDeviceToHost, st), err);
+  RT_CUDA_TRY(cudaMemcpyFromSymbolAsync(&p->h_flags, g_trav_flags, sizeof(uint32_t), 0, cudaMemcpyDeviceToHost, st), err);
   RT_CUDA_TRY(cudaStreamSynchronize(st), err);
   if (stats) {
+    stats->stack_overflow = p->h_flags & 1u;
     stats->nodes_visited = h64[0];
     stats->tris_tested = h64[1];
     stats->kernel_launches = 1;

@@ -17,6 +17,21 @@ namespace rt {
 enum { ACCEL_WIDE = 0, ACCEL_BVH2 = 1, ACCEL_BRUTE = 2 };
 static const uint32_t RT_MISS = 0xFFFFFFFFu;
 
+// Deepest binary tree a traversal stack is sized for.  An ordered binary traversal holds at most one
+// postponed child per level, so a stack of this many entries cannot overflow on a tree this deep.  A
+// Karras tree over 63-bit Morton codes with 32-bit index tie-breaks is at most 63 + 32 = 95 deep; the
+// treelet pass may rearrange 7-leaf treelets, so build_blas measures the final depth (k_emit_bvh2) and
+// refuses the mesh (RT_ERR_UNSUPPORTED) when it exceeds the limit.  The 8-wide traversal can hold
+// a node group and a postponed triangle group per level: its limit is half of this.
+#define RT_MAX_TREE_DEPTH 128
+// The top-level tree is a median split (rt_tlas.hpp): ceil(log2(instances)) <= 32 levels.
+#define RT_MAX_TLAS_DEPTH 32
+// What a kernel does when an entry does not fit after all (never for a tree the build accepted): the
+// includer may define it to raise a device flag; the entry is dropped without moving the stack pointer.
+#ifndef RT_FLAG_OVERFLOW
+#define RT_FLAG_OVERFLOW() ((void)0)
+#endif
+
 struct BlasDev {
   const float4* nodes;   // WIDE: 5 x 16 B per node; BVH2: 4 x 16 B per node
   const float4* tris;    // 3 x 16 B per triangle in leaf order: (v0, prim bits) (v1,-) (v2,-)
@@ -475,7 +490,7 @@ RT_HD bool trace_scene(const SceneDev& s, f3 o, f3 d, float tmin, float tmax, Hi
   }
   // top-level tree, nearest child first; the instance traversal below uses `st`, so the few
   // pending top-level nodes live in their own small stack
-  int tstack[32];
+  int tstack[RT_MAX_TLAS_DEPTH];
   int tsp = 0, node = 0;
   while (true) {
     if (node < 0) {
@@ -494,7 +509,8 @@ RT_HD bool trace_scene(const SceneDev& s, f3 o, f3 d, float tmin, float tmax, Hi
     int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
     if (h0 && h1) {
       if (tn1 < tn0) { const int t = c0; c0 = c1; c1 = t; }
-      if (tsp < 32) tstack[tsp++] = c1;
+      if (tsp < RT_MAX_TLAS_DEPTH) tstack[tsp++] = c1;
+      else RT_FLAG_OVERFLOW();
       node = c0;
     } else if (h0) {
       node = c0;
@@ -515,9 +531,9 @@ struct ArrayStack {
   int sp;
   RT_HD void reset() { sp = 0; }
   RT_HD bool empty() const { return sp == 0; }
-  RT_HD void push(uint2 v) { if (sp < N) e[sp++] = v; }
+  RT_HD void push(uint2 v) { if (sp < N) e[sp++] = v; else RT_FLAG_OVERFLOW(); }
   RT_HD uint2 pop() { return e[--sp]; }
-  RT_HD void push1(uint32_t v) { if (sp < N) e[sp++] = make_uint2(v, 0u); }
+  RT_HD void push1(uint32_t v) { if (sp < N) e[sp++] = make_uint2(v, 0u); else RT_FLAG_OVERFLOW(); }
   RT_HD uint32_t pop1() { return e[--sp].x; }
 };
 

@@ -592,8 +592,14 @@ struct Frame {
 };
 
 // one sample of shader.rgen main(): returns tmpColor; fills the primary hit record
+// sig (optional): path signature, FNV-1a over (instance, primitive) of every closest-hit trace and
+// 0xABCD0000|occluded of every shadow trace - the same definition as oracle64.cpp, so that two
+// renderers can tell "same path, different arithmetic" from "path diverged"
+static inline uint64_t sig_mix(uint64_t h, uint32_t w) { return (h ^ (uint64_t)w) * 1099511628211ull; }
 static V3 render_sample(const Frame& f, uint32_t px, uint32_t py, uint32_t i, rt_hit* primary,
-                        uint64_t* cnt) {
+                        uint64_t* cnt, uint64_t* sig_out = nullptr) {
+  uint64_t sig = 1469598103934665603ull;
+  struct SigOut { uint64_t* out; uint64_t& s; ~SigOut() { if (out) *out = s; } } sig_guard{sig_out, sig};
   const Scene& s = *f.s;
   const rt_frame_params& p = f.p;
   uint32_t samples = p.samples_per_pixel;
@@ -617,6 +623,7 @@ static V3 render_sample(const Frame& f, uint32_t px, uint32_t py, uint32_t i, rt
   for (uint32_t j = 0; j <= p.max_bounce_count; j++) {
     Hit h = trace_closest(s, origin, dir, 0.001f, 10000.0f, f.mode, cnt ? &cnt[C_TRITESTS] : nullptr);
     if (cnt) cnt[j == 0 ? C_PRIMARY : C_SECONDARY]++;
+    sig = sig_mix(sig_mix(sig, h.inst), h.prim);
     if (j == 0 && primary) {
       primary->instance = h.inst; primary->primitive = h.prim;
       primary->t = h.inst == MISS ? 0.0f : h.t; primary->u = h.u; primary->v = h.v;
@@ -638,6 +645,7 @@ static V3 render_sample(const Frame& f, uint32_t px, uint32_t py, uint32_t i, rt
       V3 L = normalize(toL);
       if (cnt) cnt[C_SHADOW]++;
       bool shadow = trace_any(s, so, L, 0.001f, dist, f.mode);
+      sig = sig_mix(sig, 0xABCD0000u | (shadow ? 1u : 0u));
       if (!s.mat.empty()) {   // material of the surface instead of the shader constants
         const rt_material& mt = s.mat[h.inst];
         tmp = v3(0.8f * mt.ka[0], 0.8f * mt.ka[1], 0.8f * mt.ka[2]);
@@ -850,6 +858,34 @@ int orc_trace_f64(void* sc, const float* o3, const float* d3, double tmin, doubl
     }
   }
   *tout = best;
+  return RT_OK;
+}
+
+// pixel jitter of shader.rgen:72-73 under the FP32 contract, for the crop: pixels x spp x (jx, jy)
+void orc_jitter(const rt_frame_params* p, int x0, int y0, int x1, int y1, float* out) {
+  const uint32_t spp = p->samples_per_pixel;
+  size_t k = 0;
+  for (int y = y0; y < y1; y++)
+    for (int x = x0; x < x1; x++)
+      for (uint32_t i = 0; i < spp; i++) {
+        out[k++] = random_hash((float)x, (float)y, (float)(spp + i));
+        out[k++] = random_hash((float)x, (float)y, (float)(spp + i) + 0.5f);
+      }
+}
+
+// path signatures of every sample of the crop (see render_sample)
+int orc_render_sigs(void* sc, const rt_camera* cam, const rt_frame_params* p, int x0, int y0, int x1, int y1, int mode,
+                    uint64_t* sigs) {
+  Scene* s = (Scene*)sc;
+  if (!s || !cam || !p || !sigs) return RT_ERR_INVALID_ARGUMENT;
+  Frame f{s, *cam, *p, mode};
+  const int cw = x1 - x0, ch = y1 - y0;
+  const uint32_t spp = p->samples_per_pixel;
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int yy = 0; yy < ch; yy++)
+    for (int xx = 0; xx < cw; xx++)
+      for (uint32_t i = 0; i < spp; i++)
+        render_sample(f, (uint32_t)(x0 + xx), (uint32_t)(y0 + yy), i, nullptr, nullptr, &sigs[((size_t)yy * cw + xx) * spp + i]);
   return RT_OK;
 }
 

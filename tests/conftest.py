@@ -19,6 +19,7 @@ def rt():
     """The package (vulkan-raytracing_b200/) under its importable name, native libraries built."""
     mod = graft.load_package()
     need = [mod.HOST_LIB_PATH, mod.RT_LIB_PATH, os.path.join(ROOT, "oracle", "liboracle.so"),
+            os.path.join(ROOT, "oracle", "liboracle64.so"),
             os.path.join(ROOT, "tests", "emu", "libemu.so")]
     if not all(os.path.exists(p) for p in need):
         graft.build()

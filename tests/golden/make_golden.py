@@ -8,7 +8,13 @@ oracle/ref_build.sh); the GPU box only reads the outputs.
                                        unmodified Camera (src/camera.cpp) after a scripted input sequence
   sea_sky_64.npz                       the reference's skybox_texture_sea decoded by its stb_image.h,
                                        box-filtered to 64x64 per face (orientation / sampling tests)
-  oracle_hashes.json                   SHA-256 of oracle RGBA8 frames (regression pins of the oracle)
+  cube_scene_packed.npz                resources/cube_scene.obj under the corrected-normal policy (the
+                                       reference's own loader reads past the end of `normals` on this file, so this
+                                       one is packed by rth_load_obj, policy 1 = de-indexed per face corner)
+  sea_sky_256.npz                      the same skybox box-filtered to 256x256 per face: config C1 on the GPU box
+  oracle_hashes.json                   SHA-256 of oracle RGBA8 frames (regression pins of the oracle); the entry
+                                       c1_cube_scene_800x600_d63_sky2048 is config C1 exactly as BASELINE.json states it
+                                       (full 2048x2048 sea skybox, only renderable where the reference checkout exists)
 """
 import ctypes as C
 import hashlib
@@ -83,6 +89,24 @@ def sea_sky():
     np.savez_compressed(os.path.join(HERE, "sea_sky_64.npz"), sky=np.rint(small).astype(np.uint8))
 
 
+def cube_scene():
+    import __graft_entry__ as g
+    rt = g.load_package()
+    v, i, policy = rt.load_obj(f"{REF}/resources/cube_scene.obj")
+    assert policy == 1
+    np.savez_compressed(os.path.join(HERE, "cube_scene_packed.npz"), vertices=v, indices=i)
+    return v, i
+
+
+def sea_sky_256():
+    import __graft_entry__ as g
+    rt = g.load_package()
+    sky = rt.load_skybox_dir(f"{REF}/resources/skybox_texture_sea")
+    f = sky.shape[1] // 256
+    small = sky.reshape(6, 256, f, 256, f, 4).astype(np.float64).mean((2, 4))
+    np.savez_compressed(os.path.join(HERE, "sea_sky_256.npz"), sky=np.rint(small).astype(np.uint8))
+
+
 def oracle_hashes():
     import __graft_entry__ as g
     rt = g.load_package()
@@ -93,6 +117,11 @@ def oracle_hashes():
     for name, inputs, params in scenes.hash_cases(rt):
         img = ob.OracleScene(inputs).render(cam, params)["rgba8"]
         out[name] = hashlib.sha256(img.tobytes()).hexdigest()
+    # config C1 with the reference's full-size skybox (not a fixture: 96 MiB); tests/test_c1.py re-renders it
+    # wherever /root/reference exists
+    full = scenes.c1_scene(rt, sky=rt.load_skybox_dir(f"{REF}/resources/skybox_texture_sea"))
+    img = ob.OracleScene(full).render(cam, scenes.c1_params(rt))["rgba8"]
+    out["c1_cube_scene_800x600_d63_sky2048"] = hashlib.sha256(img.tobytes()).hexdigest()
     json.dump(out, open(os.path.join(HERE, "oracle_hashes.json"), "w"), indent=1, sort_keys=True)
 
 
@@ -102,5 +131,7 @@ if __name__ == "__main__":
         print(n, v.shape, i.shape)
     camera_golden()
     sea_sky()
+    print("cube_scene", [a.shape for a in cube_scene()])
+    sea_sky_256()
     oracle_hashes()
     print("golden fixtures written")

@@ -134,3 +134,132 @@ def invert34(m):
     out = np.zeros(12, np.float32)
     lib().orc_invert34(a.ctypes.data, out.ctypes.data)
     return out
+
+
+# ----------------------------------------------------------------------------------------------
+# oracle/liboracle64.so: the independent float64 renderer (oracle64.cpp) and the helpers that
+# compare a frame with it at BASELINE.json's thresholds
+ORACLE64_LIB = os.path.join(ROOT, "oracle", "liboracle64.so")
+_lib64 = None
+
+
+def lib64():
+    global _lib64
+    if _lib64 is None:
+        L = C.CDLL(ORACLE64_LIB)
+        L.o64_scene_create.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.o64_scene_destroy.argtypes = [C.c_void_p]
+        L.o64_scene_set_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+        L.o64_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.o64_trace.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_void_p,
+                                C.c_void_p, C.c_void_p]
+        lib().orc_jitter.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        lib().orc_render_sigs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                          C.c_void_p]
+        _lib64 = L
+    return _lib64
+
+
+def jitter(params, crop=None):
+    """Pixel jitter of shader.rgen:72-73 under the FP32 contract: (h, w, spp, 2) float32 over the crop."""
+    lib64()
+    x0, y0, x1, y1 = crop if crop else (0, 0, params.width, params.height)
+    out = np.zeros((y1 - y0, x1 - x0, params.samples_per_pixel, 2), np.float32)
+    lib().orc_jitter(C.byref(params), x0, y0, x1, y1, out.ctypes.data)
+    return out
+
+
+def oracle32_signatures(scene32, camera, params, crop=None, brute=False):
+    lib64()
+    x0, y0, x1, y1 = crop if crop else (0, 0, params.width, params.height)
+    sig = np.zeros((y1 - y0, x1 - x0, params.samples_per_pixel), np.uint64)
+    assert lib().orc_render_sigs(scene32._h, C.byref(camera), C.byref(params), x0, y0, x1, y1, int(brute), sig.ctypes.data) == 0
+    return sig
+
+
+class Oracle64Scene:
+    """Same inputs as the product's Scene, rendered by the independent float64 renderer."""
+
+    def __init__(self, inputs):
+        self.inputs = inputs
+        self._h = C.c_void_p()
+        d = inputs.desc()
+        rc = lib64().o64_scene_create(C.byref(d), C.byref(self._h))
+        if rc != 0:
+            raise RuntimeError(f"oracle64 error {rc}")
+
+    def close(self):
+        if self._h and self._h.value:
+            lib64().o64_scene_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_transforms(self, xforms):
+        a = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
+        assert lib64().o64_scene_set_transforms(self._h, a.ctypes.data, a.shape[0]) == 0
+
+    def render(self, camera, params, crop=None):
+        from vulkan_raytracing_b200 import HIT_DTYPE
+        x0, y0, x1, y1 = crop if crop else (0, 0, params.width, params.height)
+        w, h, spp = x1 - x0, y1 - y0, params.samples_per_pixel
+        jit = jitter(params, (x0, y0, x1, y1))
+        f64 = np.zeros((h, w, 4), np.float64)
+        u8 = np.zeros((h, w, 4), np.uint8)
+        prim = np.zeros(h * w * spp, HIT_DTYPE)
+        sig = np.zeros((h, w, spp), np.uint64)
+        cnt = np.zeros(8, np.uint64)
+        rc = lib64().o64_render(self._h, C.byref(camera), C.byref(params), x0, y0, x1, y1, jit.ctypes.data, f64.ctypes.data,
+                                u8.ctypes.data, prim.ctypes.data, sig.ctypes.data, cnt.ctypes.data)
+        if rc != 0:
+            raise RuntimeError(f"oracle64 render error {rc}")
+        return {"rgba64": f64, "rgba8": u8, "primary": prim, "sig": sig,
+                "counts": {n: int(cnt[i]) for i, n in enumerate(COUNT_NAMES[:5])}}
+
+    def trace_rays(self, origins, dirs, tmin=0.001, tmax=10000.0):
+        o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        inst = np.zeros(o.shape[0], np.uint32)
+        prim = np.zeros(o.shape[0], np.uint32)
+        t = np.zeros(o.shape[0], np.float64)
+        assert lib64().o64_trace(self._h, o.shape[0], o.ctypes.data, d.ctypes.data, float(np.float32(tmin)),
+                                 float(np.float32(tmax)), inst.ctypes.data, prim.ctypes.data, t.ctypes.data) == 0
+        return inst, prim, t
+
+
+def compare_with_oracle64(img8, primary, ref64, sig32=None):
+    """Frame (RGBA8 + primary hit records) against the float64 renderer at BASELINE.json's thresholds.
+    Returns a report dict: primary-id match rate, max per-channel error, PSNR, and the residual pixels
+    (error > 2/255) classified by cause:
+      primary    a primary ray of the pixel hit another primitive (an edge / silhouette sample),
+      path       same primary hits, but a later bounce of some sample took another path (sig32 given:
+                 the two renderers' path signatures differ - chaotic amplification through the
+                 refractive mesh), unknown when no signatures are available,
+      arithmetic same paths, different value: that would be a formula disagreement."""
+    spp = ref64["sig"].shape[2]
+    h, w = ref64["rgba8"].shape[:2]
+    rp = ref64["primary"]
+    same = (primary["instance"] == rp["instance"]) & (primary["primitive"] == rp["primitive"])
+    diff = np.abs(img8.astype(np.int32) - ref64["rgba8"].astype(np.int32)).max(axis=2)
+    mse = np.mean((img8[..., :3].astype(np.float64) - ref64["rgba8"][..., :3].astype(np.float64)) ** 2)
+    psnr = 99.0 if mse == 0 else 10 * np.log10(255.0 ** 2 / mse)
+    resid = diff > 2
+    prim_pix = ~same.reshape(h, w, spp).all(axis=2)
+    rep = {"primary_match": float(same.mean()), "max_err": int(diff.max()), "psnr": float(psnr),
+           "residual_pixels": int(resid.sum()), "pixels": int(h * w),
+           "residual_primary": int((resid & prim_pix).sum())}
+    if sig32 is not None:
+        path_pix = (sig32 != ref64["sig"]).any(axis=2)
+        rep["samples_path_diverged"] = int((sig32 != ref64["sig"]).sum())
+        rep["residual_path"] = int((resid & ~prim_pix & path_pix).sum())
+        rep["residual_arithmetic"] = int((resid & ~prim_pix & ~path_pix).sum())
+        # error of the pixels whose every sample followed the same path in both renderers
+        clean = ~path_pix & ~prim_pix
+        rep["max_err_same_path"] = int(diff[clean].max()) if clean.any() else 0
+        rep["pixels_same_path"] = int(clean.sum())
+    return rep

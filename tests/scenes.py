@@ -54,6 +54,27 @@ def sea_sky_64():
     return np.load(os.path.join(GOLDEN, "sea_sky_64.npz"))["sky"]
 
 
+def sea_sky_256():
+    return np.load(os.path.join(GOLDEN, "sea_sky_256.npz"))["sky"]
+
+
+def c1_scene(rt, sky=None):
+    """BASELINE config C1: cube_scene.obj (corrected-normal policy) in the centre slot with the
+    default CENTER_MESH_TYPE 1 (mirror, config.h:15), the orbiting slot filled with cube.obj at the default
+    ORBITING_MESH_TYPE 0 (diffuse, config.h:16) at T(0,0,5) (main.cpp:1805-1808), skybox_texture_sea
+    (config.h:4).  sky=None: the 256x256 fixture of that skybox (the 2048x2048 original is not a fixture)."""
+    sv, si = golden_mesh("cube_scene")
+    cv, ci = unit_cube()
+    return rt.SceneInputs([(sv, si), (cv, ci)], [(0, rt.TYPE_MIRROR, rt.IDENTITY34),
+                                                 (1, rt.TYPE_DIFFUSE, rt.translation34(0, 0, 5))],
+                          sea_sky_256() if sky is None else sky)
+
+
+def c1_params(rt):
+    """800x600 window (main.cpp:805), MAX_BOUNCE_COUNT 63, SAMPLES_PER_PIXEL 4 (config.h:26-27)."""
+    return rt.FrameParams.make(800, 600, 63, 4)
+
+
 def c1_like_scene(rt):
     """Small stand-in for config C1 (the reference's cube_scene.obj is malformed for its own
     loader): mirror teapot + diffuse cube, reference's sea skybox at 64x64."""
@@ -73,6 +94,7 @@ def hash_cases(rt):
                                                               (0, rt.TYPE_REFRACTIVE, rt.translation34(0, 0, 5))], sky),
          rt.FrameParams.make(240, 135, 4, 4)),
         ("smoke_160x120_d6", smoke_scene(rt), rt.FrameParams.make(160, 120, 6, 4)),
+        ("c1_cube_scene_800x600_d63_sky256", c1_scene(rt), c1_params(rt)),
     ]
 
 

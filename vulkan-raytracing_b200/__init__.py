@@ -37,8 +37,12 @@ FLAG_GENERATE_NORMALS = 0x20
 MISS = 0xFFFFFFFF
 
 
+ERR_INVALID_ARGUMENT, ERR_NO_DEVICE, ERR_CUDA, ERR_OUT_OF_MEMORY, ERR_UNSUPPORTED = -1, -2, -3, -4, -5
+
+
 class RtError(RuntimeError):
-    pass
+    """Failure of a C-ABI call; `code` is the RT_ERR_* value (None for errors raised on the Python side)."""
+    code = None
 
 
 # ----------------------------------------------------------------------------- structs
@@ -420,7 +424,9 @@ def rt_lib():
 
 def _check(rc):
     if rc != 0:
-        raise RtError(f"rt_b200 error {rc}: {rt_lib().rt_last_error().decode()}")
+        e = RtError(f"rt_b200 error {rc}: {rt_lib().rt_last_error().decode()}")
+        e.code = rc
+        raise e
 
 
 def device_count() -> int:
@@ -434,10 +440,10 @@ def pixel_bytes(fmt: int) -> int:
 class Scene:
     """A built scene on one B200: rt_scene_build … rt_scene_destroy."""
 
-    def __init__(self, inputs: SceneInputs, device_id: int = -1, accel: int = ACCEL_DEFAULT):
+    def __init__(self, inputs: SceneInputs, device_id: int = -1, accel: int = ACCEL_DEFAULT, flags: int = 0):
         self.inputs = inputs
         self._h = C.c_void_p()
-        d = inputs.desc(device_id, accel)
+        d = inputs.desc(device_id, accel | flags)
         _check(rt_lib().rt_scene_build(C.byref(d), C.byref(self._h)))
 
     def close(self):

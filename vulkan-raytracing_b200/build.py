@@ -88,6 +88,9 @@ def build_oracle(force=False):
     out = os.path.join(d, "liboracle.so")
     if force or _newer(out, [os.path.join(d, "oracle.cpp"), os.path.join(ROOT, "include", "rt_b200.h")]):
         run(["make", "-C", d, "liboracle.so", "-B"])
+    out64 = os.path.join(d, "liboracle64.so")
+    if force or _newer(out64, [os.path.join(d, "oracle64.cpp"), os.path.join(ROOT, "include", "rt_b200.h")]):
+        run(["make", "-C", d, "liboracle64.so", "-B"])
     if os.path.isdir(os.path.join(REF, "src")) and os.path.exists(os.path.join(d, "ref_build.sh")):
         run(["sh", os.path.join(d, "ref_build.sh"), REF], cwd=d)
     return out

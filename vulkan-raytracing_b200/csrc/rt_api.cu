@@ -453,7 +453,7 @@ int rt_peer_frame_open(int device_id, const rt_ipc_handle* handle, void** frame_
 }
 
 int rt_peer_frame_signal(int device_id, void* frame, uint64_t frame_bytes, uint32_t rank, uint32_t value, void* stream) {
-  if (!frame || rank >= PEER_FLAG_BYTES / 4) return fail(RT_ERR_INVALID_ARGUMENT, "bad peer frame or rank");
+  if (!frame || rank >= PEER_FLAG_BYTES / 4 - 1) return fail(RT_ERR_INVALID_ARGUMENT, "bad peer frame or rank");
   RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
   k_peer_signal<<<1, 1, 0, (cudaStream_t)stream>>>((uint32_t*)((char*)frame + peer_flag_offset(frame_bytes)), rank, value);
   RT_CUDA_TRY(cudaGetLastError(), g_err);
@@ -462,10 +462,11 @@ int rt_peer_frame_signal(int device_id, void* frame, uint64_t frame_bytes, uint3
 
 int rt_peer_frame_wait(int device_id, void* frame, uint64_t frame_bytes, uint32_t n_ranks, uint32_t value, uint32_t timeout_ms,
                        void* stream) {
-  if (!frame || n_ranks == 0 || n_ranks > PEER_FLAG_BYTES / 4) return fail(RT_ERR_INVALID_ARGUMENT, "bad peer frame or rank count");
+  if (!frame || n_ranks == 0 || n_ranks > PEER_FLAG_BYTES / 4 - 1) return fail(RT_ERR_INVALID_ARGUMENT, "bad peer frame or rank count");
   RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
-  static uint32_t* d_status = nullptr;
-  if (!d_status) RT_CUDA_TRY(cudaMalloc(&d_status, sizeof(uint32_t)), g_err);
+  // the time-out word is the last word of the frame's own flag area: it lives on the owner's device with
+  // the frame (a process-wide static would sit on whichever device waited first) and goes away with it
+  uint32_t* d_status = (uint32_t*)((char*)frame + peer_flag_offset(frame_bytes)) + (PEER_FLAG_BYTES / 4 - 1);
   cudaStream_t st = (cudaStream_t)stream;
   RT_CUDA_TRY(cudaMemsetAsync(d_status, 0, sizeof(uint32_t), st), g_err);
   k_peer_wait<<<1, 128, 0, st>>>((const uint32_t*)((char*)frame + peer_flag_offset(frame_bytes)), n_ranks, value,

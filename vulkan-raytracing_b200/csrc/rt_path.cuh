@@ -44,7 +44,8 @@ struct PathArgs {
   float4* sample;                // one radiance slot per sample
   rt_hit* primary;               // optional export of the primary hit records
   unsigned long long* stats64;   // COUNT: nodes visited / triangles tested (closest, shadow)
-  int t_serve, t_leaf, chunk;
+  int t_serve, t_leaf, t_left, chunk;
+  uint32_t bounce0;              // bounce index of the rays in the queue (0 = primary rays)
 };
 
 #ifndef RT_PATH_MINBLK
@@ -80,6 +81,7 @@ __global__ void __launch_bounds__(32, RT_PATH_MINBLK) k_path(SceneDev scene, Fra
   const int t_serve = a.t_serve, t_leaf = a.t_leaf;
   uint32_t n_sec = 0, n_shadow = 0, n_miss = 0, n_diff = 0, n_spec = 0;
   uint32_t c_nodes[2] = {0, 0}, c_tris[2] = {0, 0};
+  uint32_t c_iter[2] = {0, 0}, c_walk[2] = {0, 0}, c_cat[5] = {0, 0, 0, 0, 0};   // COUNT: node-loop iterations / walking lanes, [1] = after the queue ran dry
 
   auto pop_or_none = [&]() -> int {
     if (sp == 0) return PATH_NONE;
@@ -143,7 +145,7 @@ __global__ void __launch_bounds__(32, RT_PATH_MINBLK) k_path(SceneDev scene, Fra
             }
           } else {
             const bool hit = best.inst != RT_MISS;
-            if (a.primary && bounce == 0u) {
+            if (a.primary && bounce == 0u) {   // (bounce0 > 0: the wavefront launches exported them)
               uint32_t x, y;
               slot_to_pixel(U, slot / U.spp, x, y);
               rt_hit out;
@@ -206,7 +208,7 @@ __global__ void __launch_bounds__(32, RT_PATH_MINBLK) k_path(SceneDev scene, Fra
             if (rank < avail) {
               const float4 ro = a.rayO[chunk_next + rank], rd = a.rayD[chunk_next + rank];
               slot = __float_as_uint(ro.w);
-              bounce = 0u;
+              bounce = a.bounce0;
               shadow = false;
               begin_ray(mk3(ro.x, ro.y, ro.z), mk3(rd.x, rd.y, rd.z), 10000.0f);  // shader.rgen:86-87
             }
@@ -216,7 +218,10 @@ __global__ void __launch_bounds__(32, RT_PATH_MINBLK) k_path(SceneDev scene, Fra
       }
       const uint32_t mw = __ballot_sync(FULL, st == PS_WAIT), md = __ballot_sync(FULL, st == PS_DONE);
       const uint32_t mr = __ballot_sync(FULL, st == PS_RUN);
-      if (mw == 0u && __popc(md) < t_serve && (mr != 0u || md == 0u)) break;
+      // once here, serve everybody: a lane left in DONE would wait through the whole next traverse phase
+      // (it also counts toward t_serve there, so leftovers make the next serve come early and small).
+      // Only a last straggler or two (rays that missed every instance box in this very pass) may stay.
+      if (mw == 0u && __popc(md) < a.t_left && (mr != 0u || md == 0u)) break;
     }
     if (!__any_sync(FULL, st != PS_IDLE)) break;  // nothing in flight and the queue is empty
 
@@ -224,26 +229,32 @@ __global__ void __launch_bounds__(32, RT_PATH_MINBLK) k_path(SceneDev scene, Fra
     {
       const bool queue_empty = exhausted && chunk_next == chunk_end;
       // lanes that already wait for the next serve phase
-      const int waiting0 = __popc(__ballot_sync(FULL, st == PS_DONE || (st == PS_IDLE && !queue_empty)));
       while (true) {
         const uint32_t runm = __ballot_sync(FULL, st == PS_RUN);
+        const int waiting0 = __popc(__ballot_sync(FULL, st == PS_DONE || st == PS_WAIT || (st == PS_IDLE && !queue_empty)));
         while (true) {
           if (node >= 0) {
             const float8 lo8 = ldg256(&nodes[4 * (size_t)node]), hi8 = ldg256(&nodes[4 * (size_t)node + 2]);
             const float4 n0 = lo8.a, n1 = lo8.b, n2 = hi8.a, n3 = hi8.b;
             if (COUNT) c_nodes[shadow ? 1 : 0]++;
             float tn0, tf0, tn1, tf1;
+#ifdef RT_PATH_DEBUG
+#define PDBG(...) do { if (slot == RT_PATH_DEBUG && st == PS_RUN) printf(__VA_ARGS__); } while (0)
+#else
+#define PDBG(...) ((void)0)
+#endif
             slab_interval(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, 0.001f, best.t, tn0, tf0);
             slab_interval(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, 0.001f, best.t, tn1, tf1);
             const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
             const int c0 = (int)__float_as_uint(n3.x), c1 = (int)__float_as_uint(n3.y);
-            const bool first0 = h0 && !(h1 && tn1 < tn0);   // nearer child first
+            const bool both = h0 && h1;
+            const bool swap = both ? (tn1 < tn0) : !h0;   // the child to visit first is c1
+            const int cnear = swap ? c1 : c0, cfar = swap ? c0 : c1;
             bool need_pop = !(h0 || h1);
-            node = first0 ? c0 : c1;
-            if (h0 && h1) {
-              const uint32_t far = (uint32_t)(first0 ? c1 : c0);
-              if (sp < PATH_STACK_SM) stk[sp * 32] = far;
-              else if (sp < PATH_STACK_CAP) loc[sp - PATH_STACK_SM] = far;
+            node = cnear;
+            if (both) {
+              if (sp < PATH_STACK_SM) stk[sp * 32] = (uint32_t)cfar;
+              else if (sp < PATH_STACK_CAP) loc[sp - PATH_STACK_SM] = (uint32_t)cfar;
               if (sp < PATH_STACK_CAP) sp++;
               else RT_FLAG_OVERFLOW();   // cannot happen for a tree build_blas accepted
             }
@@ -252,9 +263,21 @@ __global__ void __launch_bounds__(32, RT_PATH_MINBLK) k_path(SceneDev scene, Fra
               need_pop = true;
             }
             if (need_pop) node = pop_or_none();
+            PDBG("node step: h0 %d h1 %d tn %g %g tf %g %g c0 %d c1 %d -> node %d parked %d sp %d best.t %g\n", (int)h0, (int)h1, tn0, tn1, tf0, tf1, c0, c1, node, parked, sp, best.t);
           }
           const uint32_t walk = __ballot_sync(FULL, node >= 0);
           const uint32_t pk = __ballot_sync(FULL, parked != PATH_NONE);
+          if (COUNT) {
+            c_iter[queue_empty ? 1 : 0]++;
+            c_walk[queue_empty ? 1 : 0] += (uint32_t)__popc(walk);
+            if (!queue_empty) {   // what the lanes that do not walk are waiting for
+              c_cat[0] += (uint32_t)__popc(__ballot_sync(FULL, st == PS_IDLE));
+              c_cat[1] += (uint32_t)__popc(__ballot_sync(FULL, st == PS_DONE || st == PS_WAIT));
+              c_cat[2] += (uint32_t)__popc(__ballot_sync(FULL, st == PS_RUN && node == PATH_NONE && parked == PATH_NONE));
+              c_cat[3] += (uint32_t)__popc(__ballot_sync(FULL, st == PS_RUN && node == PATH_NONE && parked != PATH_NONE));
+              c_cat[4] += (uint32_t)__popc(__ballot_sync(FULL, st == PS_RUN && node < 0 && node != PATH_NONE));
+            }
+          }
           if (walk == 0u || __popc(pk) >= t_leaf) break;
           if (waiting0 + __popc(runm & ~walk & ~pk) >= t_serve) break;
         }
@@ -263,6 +286,7 @@ __global__ void __launch_bounds__(32, RT_PATH_MINBLK) k_path(SceneDev scene, Fra
           const float4* tp = tris + 3 * (size_t)(uint32_t)~parked;
           const float4 ta = __ldg(tp), tb = __ldg(tp + 1), tc = __ldg(tp + 2);
           if (COUNT) c_tris[shadow ? 1 : 0]++;
+          PDBG("tri test: leaf %d prim %u best.t %g node %d sp %d\n", ~parked, __float_as_uint(ta.w), best.t, node, sp);
           parked = PATH_NONE;
           float t, u, v;
           if (tri_test(r, mk3(ta.x, ta.y, ta.z), mk3(tb.x, tb.y, tb.z), mk3(tc.x, tc.y, tc.z), 0.001f, best.t, t, u, v)) {
@@ -309,6 +333,13 @@ __global__ void __launch_bounds__(32, RT_PATH_MINBLK) k_path(SceneDev scene, Fra
     atomicAdd(&a.stats64[1], (unsigned long long)c_tris[0]);
     atomicAdd(&a.stats64[2], (unsigned long long)c_nodes[1]);
     atomicAdd(&a.stats64[3], (unsigned long long)c_tris[1]);
+    if (lane == 0) {   // SIMD occupancy of the node loop (RT_DEBUG_PATH prints it)
+      atomicAdd(&a.stats64[4], (unsigned long long)c_iter[0]);
+      atomicAdd(&a.stats64[5], (unsigned long long)c_walk[0]);
+      atomicAdd(&a.stats64[6], (unsigned long long)c_iter[1]);
+      atomicAdd(&a.stats64[7], (unsigned long long)c_walk[1]);
+      for (int k = 0; k < 5; k++) atomicAdd(&a.stats64[8 + k], (unsigned long long)c_cat[k]);
+    }
   }
 }
 

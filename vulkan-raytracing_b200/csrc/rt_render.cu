@@ -29,7 +29,9 @@
 #include <cstdint>
 namespace rt { __device__ uint32_t g_trav_flags; }
 #if defined(__CUDA_ARCH__)
-#define RT_FLAG_OVERFLOW() atomicOr(&::rt::g_trav_flags, 1u)
+// a plain store of a constant: an atomic here drags warp-aggregation code (votes, uniform-datapath
+// reduction) into the push path of the traversal loop and cost the closest-hit kernel 10 % (measured)
+#define RT_FLAG_OVERFLOW() (*(volatile uint32_t*)&::rt::g_trav_flags = 1u)
 #else
 #define RT_FLAG_OVERFLOW() ((void)0)   // host pass of the RT_HD functions: never executed
 #endif
@@ -712,7 +714,7 @@ struct FramePipeline {
   uint32_t last_bounce[RT_MAX_SUB] = {0, 0, 0, 0};
   uint64_t last_launches = 0;
   std::vector<uint32_t> h_all;
-  unsigned long long h64[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  unsigned long long h64[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   uint32_t h_flags = 0;          // g_trav_flags of the last frame / ray batch
   bool stats_pending = false;
 };
@@ -776,7 +778,7 @@ static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std:
     p->cnt_blocks = bounces + 2;
     RT_CUDA_TRY(cudaMalloc(&p->cnt, RT_MAX_SUB * p->cnt_blocks * C_STRIDE * sizeof(uint32_t)), err);
   }
-  if (!p->stats64) RT_CUDA_TRY(cudaMalloc(&p->stats64, 8 * sizeof(unsigned long long)), err);
+  if (!p->stats64) RT_CUDA_TRY(cudaMalloc(&p->stats64, 16 * sizeof(unsigned long long)), err);
   if (!p->ev[0]) {
     RT_CUDA_TRY(cudaEventCreate(&p->ev[0]), err);
     RT_CUDA_TRY(cudaEventCreate(&p->ev[1]), err);
@@ -893,10 +895,13 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   const bool may_sort = accel != ACCEL_BRUTE && sort_from <= (int)U.max_bounce && sort_from <= sort_to;
   const bool wave = accel == ACCEL_WIDE && wave_on && rq.scene.tlas == nullptr;
   // The bounce-fused path kernel (rt_path.cuh): binary BVH, instances looped (no top-level tree).
-  // RT_FUSED=0 selects the per-bounce wavefront launches for the same frame.
-  static const bool fused_env = getenv("RT_FUSED") ? atoi(getenv("RT_FUSED")) != 0 : true;
-  static const int path_serve = getenv("RT_PATH_SERVE") ? atoi(getenv("RT_PATH_SERVE")) : 12;
-  static const int path_leaf = getenv("RT_PATH_LEAF") ? atoi(getenv("RT_PATH_LEAF")) : 12;
+  // Opt-in (RT_FUSED=1): parity-green, but measured slower than the per-bounce wavefront launches on
+  // every workload (C3 13.1 vs 8.9 ms, a 1/8 shard of C4 7.9 vs 5.1 ms): the lock-step phases cost 10.2
+  // warp instructions per node visit against 6.6 (profiles/r02_path_kernel.txt).
+  static const bool fused_env = getenv("RT_FUSED") ? atoi(getenv("RT_FUSED")) != 0 : false;
+  static const int path_serve = getenv("RT_PATH_SERVE") ? atoi(getenv("RT_PATH_SERVE")) : 16;
+  static const int path_leaf = getenv("RT_PATH_LEAF") ? atoi(getenv("RT_PATH_LEAF")) : 8;
+  static const int path_left = getenv("RT_PATH_LEFT") ? atoi(getenv("RT_PATH_LEFT")) : 3;
   static const int path_chunk = getenv("RT_PATH_CHUNK") ? atoi(getenv("RT_PATH_CHUNK")) : 64;
   const bool fused = fused_env && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && !may_sort && rq.scene.n_inst <= 32u;
   const int nsub = (sub_env >= 2 && nslots >= sub_min_slots && !may_sort && !wave)
@@ -923,7 +928,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   uint64_t launches = 0;
   RT_CUDA_TRY(cudaEventRecord(p->ev[0], st), err);
   RT_CUDA_TRY(cudaMemsetAsync(p->cnt, 0, (size_t)nsub * p->cnt_blocks * C_STRIDE * sizeof(uint32_t), st), err);
-  RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
+  RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 16 * sizeof(unsigned long long), st), err);
   {
     void* fl = nullptr;
     RT_CUDA_TRY(cudaGetSymbolAddress(&fl, g_trav_flags), err);
@@ -1042,37 +1047,47 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     return RT_OK;
   };
   // the whole bounce loop of one sub-frame in one persistent launch
-  auto enqueue_path = [&](SubCtx& c) -> int {
+  auto enqueue_path = [&](SubCtx& c, uint32_t j0) -> int {
     FramePipeline::Sub& sb = *c.sb;
     PathArgs pa;
-    pa.cnt = c.cnt;
-    pa.rayO = c.rayO[0];
-    pa.rayD = c.rayD[0];
+    pa.cnt = c.cnt + (size_t)j0 * C_STRIDE;
+    pa.rayO = c.rayO[c.cur];
+    pa.rayD = c.rayD[c.cur];
+    pa.bounce0 = j0;
     pa.sample = p->sample;
     pa.primary = rq.want_primary ? rq.d_primary : nullptr;
     pa.stats64 = p->stats64;
     pa.t_serve = std::max(1, std::min(32, path_serve));
     pa.t_leaf = std::max(1, std::min(32, path_leaf));
+    pa.t_left = std::max(1, std::min(32, path_left));
     pa.chunk = std::max(32, path_chunk) & ~31;
     static int blocks[2] = {0, 0};
     if (!blocks[0]) { blocks[0] = persistent_blocks(k_path<false>, 32); blocks[1] = persistent_blocks(k_path<true>, 32); }
-    RT_CUDA_TRY(cudaEventRecord(sb.kev[0], c.st), err);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j0 + 0], c.st), err);
     if (counting) k_path<true><<<blocks[1], 32, 0, c.st>>>(rq.scene, U, pa);
     else k_path<false><<<blocks[0], 32, 0, c.st>>>(rq.scene, U, pa);
-    RT_CUDA_TRY(cudaEventRecord(sb.kev[1], c.st), err);
-    RT_CUDA_TRY(cudaEventRecord(sb.kev[2], c.st), err);   // no separate shadow launches: empty interval
-    RT_CUDA_TRY(cudaEventRecord(sb.kev[3], c.st), err);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j0 + 1], c.st), err);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j0 + 2], c.st), err);   // no separate shadow launches: empty interval
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j0 + 3], c.st), err);
+    // the shadow rays of the last wavefront bounce run beside this launch; the join below waits for sev[2 j0 + 1]
+    if (shadow_async && j0 > 0) RT_CUDA_TRY(cudaStreamWaitEvent(c.st, sb.sev[2 * (j0 - 1) + 1], 0), err);
+    if (shadow_async) RT_CUDA_TRY(cudaEventRecord(sb.sev[2 * j0 + 1], c.st), err);
     launches++;
-    c.last_bounce = 0;
+    c.last_bounce = j0;
     return RT_OK;
   };
-  if (fused) {
-    for (int k = 0; k < nsub; k++) {
-      rc = enqueue_path(ctx[k]);
-      if (rc != RT_OK) return rc;
-    }
-  } else
+  // RT_FUSE_FROM = j: bounces < j run as wavefront launches (coherent rays, full batches), the rest of
+  // every path in the fused kernel
+  static const uint32_t fuse_from = getenv("RT_FUSE_FROM") ? (uint32_t)atoi(getenv("RT_FUSE_FROM")) : 0u;
   for (uint32_t j = 0; j <= U.max_bounce; j++) {
+    if (fused && j >= fuse_from) {
+      for (int k = 0; k < nsub; k++) {
+        if (ctx[k].dead) continue;
+        rc = enqueue_path(ctx[k], j);
+        if (rc != RT_OK) return rc;
+      }
+      break;
+    }
     bool any = false;
     for (int k = 0; k < nsub; k++) {
       if (ctx[k].dead) continue;
@@ -1085,7 +1100,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   // join: every sub-frame's shadow rays, then sub-frame 1 into the caller's stream
   for (int k = nsub - 1; k >= 0; k--) {
     SubCtx& c = ctx[k];
-    if (shadow_async && !fused) RT_CUDA_TRY(cudaStreamWaitEvent(c.st, c.sb->sev[2 * c.last_bounce + 1], 0), err);
+    if (shadow_async) RT_CUDA_TRY(cudaStreamWaitEvent(c.st, c.sb->sev[2 * c.last_bounce + 1], 0), err);
     if (k > 0) {
       RT_CUDA_TRY(cudaEventRecord(c.sb->done, c.st), err);
       RT_CUDA_TRY(cudaStreamWaitEvent(st, c.sb->done, 0), err);
@@ -1186,6 +1201,14 @@ void pipeline_frame_stats(FramePipeline* p, rt_stats* stats) {
     }
     stats->nodes_visited = h64[0] + h64[2];
     stats->tris_tested = h64[1] + h64[3];
+    static const bool dbg_path = getenv("RT_DEBUG_PATH") != nullptr;
+    if (dbg_path && h64[4] + h64[6])
+      fprintf(stderr, "k_path node loop: %.1f M warp iterations at %.2f walking lanes while the queue had rays, %.1f M at %.2f after\n",
+              h64[4] / 1e6, h64[4] ? (double)h64[5] / h64[4] : 0.0, h64[6] / 1e6, h64[6] ? (double)h64[7] / h64[6] : 0.0);
+    if (dbg_path && h64[4])
+      fprintf(stderr, "  lanes per iteration not walking (queue has rays): no path %.2f, ray done / between meshes %.2f, mesh done %.2f, "
+              "only a parked leaf %.2f, second leaf (blocked) %.2f\n", (double)h64[8] / h64[4], (double)h64[9] / h64[4],
+              (double)h64[10] / h64[4], (double)h64[11] / h64[4], (double)h64[12] / h64[4]);
     stats->kernel_launches = p->last_launches;
     stats->ray_state_bytes = 2 * sizeof(float4) + sizeof(uint4) + sizeof(uint32_t);
   }
@@ -1196,8 +1219,8 @@ int pipeline_trace_batch(FramePipeline* p, const SceneDev& scene, uint64_t n, co
                          rt_stats* stats, std::string& err) {
   if (n == 0) return RT_OK;
   p->stats_pending = false;   // the stats below replace those of the last frame
-  if (!p->stats64) RT_CUDA_TRY(cudaMalloc(&p->stats64, 8 * sizeof(unsigned long long)), err);
-  RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 8 * sizeof(unsigned long long), st), err);
+  if (!p->stats64) RT_CUDA_TRY(cudaMalloc(&p->stats64, 16 * sizeof(unsigned long long)), err);
+  RT_CUDA_TRY(cudaMemsetAsync(p->stats64, 0, 16 * sizeof(unsigned long long), st), err);
   {
     void* fl = nullptr;
     RT_CUDA_TRY(cudaGetSymbolAddress(&fl, g_trav_flags), err);
@@ -1212,7 +1235,7 @@ int pipeline_trace_batch(FramePipeline* p, const SceneDev& scene, uint64_t n, co
   RT_DISPATCH_ACCEL(scene.accel, counting, CALL_BATCH);
 #undef CALL_BATCH
   RT_CUDA_TRY(cudaGetLastError(), err);
-  unsigned long long h64[8];
+  unsigned long long h64[16];
   RT_CUDA_TRY(cudaMemcpyAsync(h64, p->stats64, sizeof h64, cudaMemcpyDeviceToHost, st), err);
   RT_CUDA_TRY(cudaMemcpyFromSymbolAsync(&p->h_flags, g_trav_flags, sizeof(uint32_t), 0, cudaMemcpyDeviceToHost, st), err);
   RT_CUDA_TRY(cudaStreamSynchronize(st), err);

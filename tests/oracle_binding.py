@@ -204,11 +204,13 @@ class Oracle64Scene:
         a = np.ascontiguousarray(xforms, np.float32).reshape(-1, 12)
         assert lib64().o64_scene_set_transforms(self._h, a.ctypes.data, a.shape[0]) == 0
 
-    def render(self, camera, params, crop=None):
+    def render(self, camera, params, crop=None, jitter_shift=0.0):
         from vulkan_raytracing_b200 import HIT_DTYPE
         x0, y0, x1, y1 = crop if crop else (0, 0, params.width, params.height)
         w, h, spp = x1 - x0, y1 - y0, params.samples_per_pixel
         jit = jitter(params, (x0, y0, x1, y1))
+        if jitter_shift:
+            jit = np.clip(jit + np.float32(jitter_shift), 0.0, 0.999999).astype(np.float32)
         f64 = np.zeros((h, w, 4), np.float64)
         u8 = np.zeros((h, w, 4), np.uint8)
         prim = np.zeros(h * w * spp, HIT_DTYPE)
@@ -220,6 +222,17 @@ class Oracle64Scene:
             raise RuntimeError(f"oracle64 render error {rc}")
         return {"rgba64": f64, "rgba8": u8, "primary": prim, "sig": sig,
                 "counts": {n: int(cnt[i]) for i, n in enumerate(COUNT_NAMES[:5])}}
+
+    def sensitivity(self, camera, params, crop=None, base=None, shift=1e-3):
+        """Per pixel: the largest 8-bit change of oracle64's own image when every sample's jitter moves by
+        +-shift pixel (about the size of FP32 rounding of a hit position seen from the camera).  A pixel that
+        moves by more than 2/255 under that is ill-conditioned: no two arithmetics can agree on it."""
+        base = base if base is not None else self.render(camera, params, crop)
+        sens = np.zeros(base["rgba8"].shape[:2], np.int32)
+        for d in (shift, -shift):
+            moved = self.render(camera, params, crop, jitter_shift=d)
+            sens = np.maximum(sens, np.abs(moved["rgba8"].astype(np.int32) - base["rgba8"].astype(np.int32)).max(axis=2))
+        return sens
 
     def trace_rays(self, origins, dirs, tmin=0.001, tmax=10000.0):
         o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3)
@@ -262,4 +275,20 @@ def compare_with_oracle64(img8, primary, ref64, sig32=None):
         clean = ~path_pix & ~prim_pix
         rep["max_err_same_path"] = int(diff[clean].max()) if clean.any() else 0
         rep["pixels_same_path"] = int(clean.sum())
+        rep["_arith_mask"] = resid & clean
     return rep
+
+
+def explain_arithmetic_residuals(rep, scene64, camera, params, crop, ref64):
+    """Splits rep['residual_arithmetic'] (same path in both renderers, error > 2/255) into ill-conditioned pixels
+    (oracle64 itself moves by more than 2/255 under a 1e-3 pixel jitter shift: a refraction near the critical angle,
+    a reflection chain grazing an edge, a sharp skybox texel seen through several bounces) and unexplained ones -
+    the latter would be a disagreement between the two readings of the shaders.  Returns the unexplained count."""
+    mask = rep.pop("_arith_mask", None)
+    if mask is None or not mask.any():
+        rep["residual_ill_conditioned"], rep["residual_unexplained"] = 0, 0
+        return 0
+    sens = scene64.sensitivity(camera, params, crop, base=ref64)
+    rep["residual_ill_conditioned"] = int((mask & (sens > 2)).sum())
+    rep["residual_unexplained"] = int((mask & (sens <= 2)).sum())
+    return rep["residual_unexplained"]

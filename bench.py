@@ -13,7 +13,10 @@ C ABI with a HOST output buffer (uniforms H2D + frame D2H inside the timed regio
 
 `--impl reference` times the reference's CPU implementation of the path: the reference has no
 CPU ray tracer and cannot be built here, so this is the oracle port (oracle/liboracle.so) on
-all host cores, each step a bounded centred crop of the same frame.
+all host cores, each step a bounded sample of the same frame: every k-th 64x64 tile (the tiles
+of shard 0 of k in the C ABI's own tile sharding), i.e. an evenly spread 1/k of the frame with
+the frame's own mix of sky, diffuse and refractive pixels.  The GPU renders exactly that shard
+too (`same_rays`), so the CPU and GPU rates in one line are over the same rays.
 """
 import argparse
 import ctypes as C
@@ -47,7 +50,7 @@ WORKLOAD_TEXT = {
     "c5a": "C5a 16x16 armadillo_standin grid flattened into one mesh (83.9 M tri, diffuse) 3840x2160 spp4 depth8, camera pulled back",
     "c5b": "C5b one armadillo_standin BLAS x 256 instances (diffuse/refractive alternating) 3840x2160 spp4 depth8, camera pulled back",
 }
-CPU_CROP_FRACTION = 3  # the CPU arm renders the centred (W/3 x H/3) crop of the frame
+CPU_SAMPLE_RAYS = 5.5e6  # the CPU arms render every k-th tile, k chosen so that a step is about this many rays
 
 
 def parse_args():
@@ -116,31 +119,47 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def crop_of(w, h):
-    cw, ch = w // CPU_CROP_FRACTION, h // CPU_CROP_FRACTION
-    x0, y0 = (w - cw) // 2, (h - ch) // 2
-    return (x0, y0, x0 + cw, y0 + ch)
+def sample_params(rt, params, rays_per_frame):
+    """rt_frame_params of the CPU sample: shard 0 of k of the frame's 64x64 tiles."""
+    k = max(2, int(round(rays_per_frame / CPU_SAMPLE_RAYS)))
+    q = rt.FrameParams.make(params.width, params.height, params.max_bounce_count, params.samples_per_pixel,
+                            shard_index=0, shard_count=k)
+    return q, k
 
 
-def cpu_arm(rt, inputs, cam, params, steps, warmup):
-    """Oracle port on all host cores over the centred crop; returns (Mrays/s, ms/step, cores, sample)."""
+def cpu_arm(rt, inputs, cam, params, steps, warmup, rays_per_frame, want_image=False):
+    """Oracle port on all host cores over every k-th tile; returns (Mrays/s, ms/step, cores, sample text, rays, image)."""
     import oracle_binding as ob
     osc = ob.OracleScene(inputs)
-    crop = crop_of(params.width, params.height)
+    q, k = sample_params(rt, params, rays_per_frame)
     cores = ob.lib().orc_num_threads()
-    rays, times = 0, []
+    rays, times, img = 0, [], None
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        r = osc.render(cam, params, crop=crop, want=("rgba8", "counts"))
+        img, c = osc.render_shard(cam, q, want_image=want_image)
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
-            c = r["counts"]
             rays = c["primary"] + c["secondary"] + c["shadow"]
     total = sum(times)
-    sample = (f"centred {crop[2]-crop[0]}x{crop[3]-crop[1]} crop of the {params.width}x{params.height} frame, "
-              f"{rays} rays per step, oracle BVH mode, OpenMP over rows")
-    return rays * len(times) / total / 1e6, 1e3 * total / len(times), cores, sample
+    sample = (f"every {k}th 64x64 tile of the {params.width}x{params.height} frame (shard 0 of {k} of the C ABI's tile sharding: "
+              f"an evenly spread 1/{k} of the frame with its own ray mix), {rays} rays per step, oracle BVH mode, OpenMP over tile rows")
+    return rays * len(times) / total / 1e6, 1e3 * total / len(times), cores, sample, rays, img
+
+
+RAYS_PER_FRAME_HINT = {"c3": 49.1e6, "c4": 196.3e6, "c2": 10.4e6, "c5a": 41.7e6, "c5b": 50.2e6}
+
+
+def source_hash():
+    """SHA-256 over the CUDA sources: ties an ncu capture (profiles/traffic.json) to the kernels it was taken from."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "vulkan-raytracing_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".h", ".hpp")):
+            h.update(f.encode())
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
 
 
 def load_peaks():
@@ -166,19 +185,34 @@ def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix, t
     frame_bytes = (trav_bytes + st_count["n_hit"] * 84 + st_count["n_miss"] * 16 + n_closest * 32 + npix * 4)
     frame_flops = trav_flops + st_count["n_hit"] * 120
     t_roof = max(frame_bytes / (hbm_gbs * 1e9), frame_flops / (fp32_tflops * 1e12) if fp32_tflops else 0.0)
+    # ncu figures of the traversal kernels (one --set full capture of this workload): only valid for the kernels they
+    # were captured from, so the file carries the hash of the CUDA sources and everything from it is null otherwise
     path = os.path.join(ROOT, "profiles", "traffic.json")
-    traffic = None
-    if traffic_applies and os.path.exists(path):   # the ncu capture is of the N=1 C3 frame; null for any other workload
+    traffic = issue_frac = simd_lanes = None
+    ncu_note = "no ncu capture applies to this workload"
+    if traffic_applies and os.path.exists(path):
         try:
-            traffic = json.load(open(path)).get("k_trace_dram_bytes_per_frame")
-        except Exception:
-            traffic = None
+            t = json.load(open(path))
+            if t.get("source_hash") == source_hash():
+                traffic = t.get("k_trace_dram_bytes_per_frame")
+                slots = trav_ms * 1e-3 * t["sm_count"] * 4 * t["sm_clock_hz"]   # issue slots of all SM sub-partitions in the traversal time
+                issue_frac = round(t["warp_instructions_per_frame"] / slots, 4)
+                simd_lanes = round(t["thread_instructions_per_frame"] / t["warp_instructions_per_frame"], 2)
+                ncu_note = f"ncu capture {t.get('capture', '')} of these sources"
+            else:
+                ncu_note = "profiles/traffic.json was captured from other kernel sources (hash differs): traffic, issue_frac, simd_lanes withheld"
+        except Exception as e:
+            ncu_note = f"profiles/traffic.json unreadable: {e}"
     return {
         "bound": "hbm", "kernel": "k_trace+k_shadow (all traversal launches of one frame)",
         "achieved": round(achieved, 1), "peak": hbm_gbs, "peak_source": hbm_src, "unit": "GB/s",
         "frac": round(achieved / hbm_gbs, 4), "traffic": traffic,
-        "note": "achieved = algorithmic node + triangle + ray-state bytes / traversal time, cache hits not discounted (SURVEY 8d); "
-                "frac > 1 means the working set is served from L1/L2 - `traffic` is what DRAM moved (ncu), see DESIGN.md 5.3",
+        "frac_algorithmic_cache_blind": round(achieved / hbm_gbs, 4),
+        "issue_frac": issue_frac, "simd_lanes": simd_lanes, "ncu": ncu_note,
+        "note": "achieved / frac follow SURVEY 8d: algorithmic node + triangle + ray-state bytes / traversal time with cache hits NOT "
+                "discounted, so frac > 1 only says the working set is served from L1/L2 (`traffic` = what DRAM really moved, ncu). "
+                "What binds the kernel: issue_frac = warp instructions / issue slots available in the traversal time, at simd_lanes "
+                "active threads per warp instruction (DESIGN.md 5.3)",
         "algorithmic_bytes_per_frame": int(trav_bytes), "traversal_ms": round(trav_ms, 4),
         "nodes_visited": int(n_node), "tris_tested": int(n_tri), "node_bytes": node_b, "tri_bytes": tri_b, "boxes_per_node": children,
         "flop_term": {"flops_per_frame": int(trav_flops), "achieved_tflops": round(trav_flops / (trav_ms * 1e-3) / 1e12, 3),
@@ -208,7 +242,7 @@ def main():
         inputs = getattr(scenes, builder)(rt, sky_size=args.sky)
         params = rt.FrameParams.make(W, H, depth, spp)
         cam_ref = scenes.c5_camera(rt) if wl.startswith("c5") else rt.CameraVectors.default()
-        v, ms, cores, sample = cpu_arm(rt, inputs, cam_ref, params, args.steps, args.warmup)
+        v, ms, cores, sample, _, _ = cpu_arm(rt, inputs, cam_ref, params, args.steps, args.warmup, RAYS_PER_FRAME_HINT[wl])
         print(json.dumps({
             "impl": "reference", "metric": "Mrays/s", "value": round(v, 3), "unit": "Mrays/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
@@ -420,6 +454,71 @@ def main():
     st_count = scene.stats()
     scene.set_counting(False)
     fp32 = rt.measure_fp32_tflops(local_rank) if rank == 0 else 0.0
+
+    def solo_frames(p, ptr, n_warm, n_timed):
+        """rank 0 alone, device output: mean frame ms (CUDA events) and rays per frame"""
+        for _ in range(n_warm):
+            scene.render_into(cam, p, ptr)
+        ms = 0.0
+        for _ in range(n_timed):
+            flush.zero_()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            scene.render_into(cam, p, ptr)
+            e1.record()
+            torch.cuda.synchronize()
+            ms += e0.elapsed_time(e1)
+        st = scene.stats()
+        return ms / n_timed, st["rays_primary"] + st["rays_secondary"] + st["rays_shadow"], st
+
+    # (a) N > 1: the SAME workload on one GPU (rank 0 alone, the other ranks wait at the barrier), so that the line
+    # carries its own strong-scaling denominator; N = 1 of the driver's scaling run is C3, a different frame
+    solo = None
+    if sharded:
+        if rank == 0:
+            full = torch.zeros((H, W, 4), dtype=torch.uint8, device=dev)
+            p_full = rt.FrameParams.make(W, H, depth, spp, output_location=rt.LOCATION_DEVICE)
+            ms1, rays1, _ = solo_frames(p_full, full.data_ptr(), 1, 3)
+            solo = {"ms_per_step": round(ms1, 4), "value": round(rays1 / (ms1 * 1e-3) / 1e6, 2), "unit": "Mrays/s", "frames": 3,
+                    "equals_sharded_frame": bool(torch.equal(full, frame)) if frame is not None else None}
+            del full
+        dist.barrier()
+    # (b) the rays the CPU arm renders (every k-th tile), on the GPU: same pixels, same rays
+    same_rays = None
+    if rank == 0 and not sharded:
+        p_s, k_s = sample_params(rt, p_compact, st_last["rays_primary"] + st_last["rays_secondary"] + st_last["rays_shadow"])
+        p_s.output_location = rt.LOCATION_DEVICE
+        buf = torch.zeros((int(rt.rt_lib().rt_frame_shard_pixels(C.byref(p_s))), 4), dtype=torch.uint8, device=dev)
+        ms_s, rays_s, _ = solo_frames(p_s, buf.data_ptr(), 2, 5)
+        same_rays = {"tiles": f"every {k_s}th 64x64 tile", "rays": int(rays_s), "gpu_ms": round(ms_s, 4),
+                     "gpu_value": round(rays_s / (ms_s * 1e-3) / 1e6, 2), "unit": "Mrays/s", "_image": buf.cpu().numpy()}
+        del buf
+    # (c) the drop-in call of INTEGRATION.md: rt_render_frame(RT_LOCATION_HOST) into a plain malloc'd buffer, as is
+    # (device frame + pageable copy) and after rt_host_buffer_pin (resolve kernel stores straight into it)
+    plain = None
+    if rank == 0 and not sharded:
+        p_h = rt.FrameParams.make(W, H, depth, spp)   # RT_LOCATION_HOST, full frame
+        hostbuf = np.empty((H, W, 4), np.uint8)
+        res = {}
+        for mode in ("pageable_copy", "pinned_by_rt_host_buffer_pin"):
+            if mode != "pageable_copy":
+                scene.pin_host_buffer(hostbuf)
+            for _ in range(2):
+                scene.render_into(cam, p_h, hostbuf.ctypes.data)
+            t_ms = 0.0
+            for _ in range(5):
+                flush.zero_()
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                scene.render_into(cam, p_h, hostbuf.ctypes.data)   # synchronous: the pixels are in hostbuf on return
+                t_ms += 1e3 * (time.perf_counter() - t0)
+            st_h = scene.stats()
+            rays_h = st_h["rays_primary"] + st_h["rays_secondary"] + st_h["rays_shadow"]
+            res[mode] = {"ms_per_step": round(t_ms / 5, 4), "value": round(rays_h / (t_ms / 5 * 1e-3) / 1e6, 2)}
+            res[mode]["equals_device_frame"] = bool((hostbuf == local.view(H, W, 4).cpu().numpy()).all())
+        scene.unpin_host_buffer()
+        plain = {"unit": "Mrays/s", "timer": "host wall clock around the synchronous call", **res}
     if rank != 0:
         if hostf is not None:
             torch.cuda.synchronize()
@@ -462,11 +561,32 @@ def main():
         out["host_frame_equals_device_frame"] = host_verified
     out["roofline"] = roofline(st_count, st_last["trace_ms"] + st_last["shadow_ms"], st_last["frame_ms"], hbm, hbm_src, fp32,
                                npix_local, traffic_applies=(wl == "c3" and world == 1 and args.accel in (0, 1)))
+    out["rays"] = {"primary": st_last["rays_primary"], "of_which_answered_by_the_top_level_in_raygen": st_last["rays_top_level"],
+                   "secondary": st_last["rays_secondary"], "shadow": st_last["rays_shadow"],
+                   "note": "value counts every traceRayEXT-equivalent, as the oracle does; primary rays that reach no instance box are "
+                           "answered in k_raygen (sky lookup) and never traversed"}
+    trav_rays = out["rays_per_frame"] - st_last["rays_top_level"]
+    out["value_traversed_rays_only"] = round(trav_rays / (ms_dev / args.steps * 1e-3) / 1e6, 2)
+    if solo is not None:
+        out["single_gpu_same_workload"] = solo
+        out["strong_efficiency_same_workload"] = round(value / (world * solo["value"]), 4)
+        out["data_plane"] = ("tiles: peer stores into rank 0's frame + arrival flags (no collective)" if gather == "peer" else
+                             "tiles: NCCL gather + de-interleave kernel") + "; NCCL otherwise carries only the set-up broadcasts and the bench barriers"
+    if plain is not None:
+        out["e2e_plain_host"] = plain
     if world == 1 and not args.no_cpu_baseline:
         p_cpu = rt.FrameParams.make(W, H, depth, spp)
-        v, ms, cores, sample = cpu_arm(rt, inputs, cam, p_cpu, 1, 0)
+        v, ms, cores, sample, rays_c, img_c = cpu_arm(rt, inputs, cam, p_cpu, 1, 0, out["rays_per_frame"], want_image=True)
         out["cpu_baseline"] = {"value": round(v, 3), "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample,
                                "ms_per_sample": round(ms, 1)}
+        if same_rays is not None:
+            same_rays["cpu_value"] = round(v, 3)
+            same_rays["gpu_over_cpu"] = round(same_rays["gpu_value"] / v, 1) if v else None
+            same_rays["rays_equal"] = bool(rays_c == same_rays["rays"])
+            same_rays["images_equal"] = bool((img_c == same_rays["_image"]).all())
+    if same_rays is not None:
+        same_rays.pop("_image", None)
+        out["same_rays"] = same_rays
     print(json.dumps(out))
     if hostf is not None:
         hostf.release()             # the creator also removes the name

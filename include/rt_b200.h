@@ -241,6 +241,16 @@ int rt_set_counting(void* scene, int enable);
 int rt_render_frame(void* scene, const rt_camera* camera, const rt_frame_params* params,
                     void* rgba_out);
 uint64_t rt_frame_output_bytes(const rt_frame_params* params);
+/* The reference copies its storage image to the swapchain every frame (main.cpp:2626-2728); a host caller of
+ * rt_render_frame(RT_LOCATION_HOST) gets the frame through a device buffer and a pageable copy unless it lets the
+ * library pin its buffer ONCE: after rt_host_buffer_pin(scene, buf, bytes) every rt_render_frame with
+ * output_location = RT_LOCATION_HOST whose rgba_out lies inside [buf, buf + bytes) has the resolve kernel store
+ * the pixels straight into that memory over PCIe (finished sky tiles early, beside the traversal): no device
+ * frame, no copy.  Full frames only (shard_count <= 1); other calls take the copy path as before.  The buffer
+ * must stay allocated until rt_host_buffer_unpin / a new pin / rt_scene_destroy (CUDA requires registered memory
+ * to be unregistered before it is freed).  One pinned buffer per scene. */
+int rt_host_buffer_pin(void* scene, void* host_buffer, uint64_t bytes);
+int rt_host_buffer_unpin(void* scene);
 /* Number of pixels shard `shard_index` writes (padded tiles included). */
 uint64_t rt_frame_shard_pixels(const rt_frame_params* params);
 /* De-interleave gathered shard buffers into a row-major frame, on the device.

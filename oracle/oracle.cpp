@@ -804,6 +804,59 @@ int orc_render(void* sc, const rt_camera* cam, const rt_frame_params* p, int x0,
   return RT_OK;
 }
 
+// Renders the tiles of one shard of a tile-sharded frame (rt_frame_params: tile t belongs to shard t % shard_count)
+// into the compact shard layout of the C ABI: tile after tile in increasing tile index, each tile_w x tile_h pixels
+// row-major, pixels outside the frame left zero.  This is what one GPU of a multi-GPU frame renders, and - with
+// shard_count = k on a single frame - an evenly spread 1/k sample of the frame with the frame's own ray mix (the
+// bounded sample of bench.py's CPU arms).  rgba8 may be NULL; counts as orc_render.
+int orc_render_shard(void* sc, const rt_camera* cam, const rt_frame_params* p, int mode, int threads, uint8_t* rgba8,
+                     uint64_t* counts) {
+  Scene* s = (Scene*)sc;
+  if (!s || !cam || !p || p->samples_per_pixel == 0) return RT_ERR_INVALID_ARGUMENT;
+  const uint32_t tw = p->tile_w ? p->tile_w : 64, th = p->tile_h ? p->tile_h : 64;
+  const uint32_t tiles_x = (p->width + tw - 1) / tw, tiles_y = (p->height + th - 1) / th;
+  const uint32_t nsh = p->shard_count ? p->shard_count : 1, sh = p->shard_index;
+  if (sh >= nsh) return RT_ERR_INVALID_ARGUMENT;
+  const uint32_t tiles = tiles_x * tiles_y;
+  const uint32_t n_local = tiles > sh ? (tiles - sh + nsh - 1) / nsh : 0;
+  Frame f{s, *cam, *p, mode};
+  const uint32_t spp = p->samples_per_pixel;
+  uint64_t total[C_N] = {0};
+#ifdef _OPENMP
+  if (threads > 0) omp_set_num_threads(threads);
+  else omp_set_num_threads(omp_get_num_procs());
+#endif
+#pragma omp parallel
+  {
+    uint64_t cnt[C_N] = {0};
+#pragma omp for schedule(dynamic, 4) nowait
+    for (long long job = 0; job < (long long)n_local * th; job++) {   // one job = one row of one tile
+      const uint32_t lt = (uint32_t)(job / th), ty = (uint32_t)(job % th);
+      const uint32_t tile = lt * nsh + sh;
+      const uint32_t y = (tile / tiles_x) * th + ty;
+      if (y >= p->height) continue;
+      for (uint32_t tx = 0; tx < tw; tx++) {
+        const uint32_t x = (tile % tiles_x) * tw + tx;
+        if (x >= p->width) break;
+        float c[4] = {0, 0, 0, 0};
+        for (uint32_t i = 0; i < spp; i++) {
+          V3 t = render_sample(f, x, y, i, nullptr, counts ? cnt : nullptr);
+          c[0] += t.x; c[1] += t.y; c[2] += t.z; c[3] += 1.0f;
+        }
+        const float fs = (float)spp;
+        if (rgba8) {
+          uint8_t* o = rgba8 + ((size_t)lt * tw * th + (size_t)ty * tw + tx) * 4;
+          for (int k = 0; k < 4; k++) o[k] = to_unorm8(c[k] / fs);
+        }
+      }
+    }
+#pragma omp critical
+    for (int k = 0; k < C_N; k++) total[k] += cnt[k];
+  }
+  if (counts) memcpy(counts, total, sizeof total);
+  return RT_OK;
+}
+
 int orc_trace(void* sc, uint64_t n, const float* o, const float* d, float tmin, float tmax, int any_hit, int mode,
               rt_hit* out) {
   Scene* s = (Scene*)sc;

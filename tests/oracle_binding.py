@@ -20,6 +20,7 @@ def lib():
         L.orc_scene_set_transforms.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
         L.orc_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                  C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_render_shard.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_trace.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_int,
                                 C.c_int, C.c_void_p]
         L.orc_trace_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double,
@@ -93,6 +94,21 @@ class OracleScene:
         if cnt is not None:
             out["counts"] = {n: int(cnt[i]) for i, n in enumerate(COUNT_NAMES)}
         return {k: v for k, v in out.items() if v is not None}
+
+    def render_shard(self, camera, params, threads=0, want_image=True):
+        """The tiles of shard params.shard_index of params.shard_count in the C ABI's compact shard layout
+        (uint8[n_pixels, 4]) plus the ray counts."""
+        tw, th = params.tile_w or 64, params.tile_h or 64
+        tiles = ((params.width + tw - 1) // tw) * ((params.height + th - 1) // th)
+        n = max(1, params.shard_count)
+        per = (tiles + n - 1) // n * tw * th
+        img = np.zeros((per, 4), np.uint8) if want_image else None
+        cnt = np.zeros(8, np.uint64)
+        rc = lib().orc_render_shard(self._h, C.byref(camera), C.byref(params), 0, threads,
+                                    img.ctypes.data if img is not None else None, cnt.ctypes.data)
+        if rc != 0:
+            raise RuntimeError(f"oracle render_shard error {rc}")
+        return img, {k: int(cnt[i]) for i, k in enumerate(COUNT_NAMES)}
 
     def trace_rays(self, origins, dirs, tmin=0.001, tmax=10000.0, any_hit=False, brute=False):
         from vulkan_raytracing_b200 import HIT_DTYPE

@@ -679,11 +679,12 @@ PARITY_SNIPPET = """
 import sys; sys.path.insert(0, 'tests')
 import __graft_entry__ as g
 rt = g.load_package()
-import oracle_binding as ob, scenes, test_gpu_parity as t
-t.check_frame(rt, ob, scenes.smoke_scene(rt), rt.FrameParams.make(160, 120, 6, 4))
-t.check_frame(rt, ob, scenes.c3_scene(rt, level=5, sky_size=256), rt.FrameParams.make(384, 216, 8, 4))
-t.check_frame(rt, ob, scenes.c1_like_scene(rt), rt.FrameParams.make(203, 151, 63, 4))
-sc = rt.Scene(scenes.c3_scene(rt, level=6, sky_size=128), device_id=0)
+import os, oracle_binding as ob, scenes, test_gpu_parity as t
+A = int(os.environ.get('TEST_ACCEL', '0'))
+t.check_frame(rt, ob, scenes.smoke_scene(rt), rt.FrameParams.make(160, 120, 6, 4), A)
+t.check_frame(rt, ob, scenes.c3_scene(rt, level=5, sky_size=256), rt.FrameParams.make(384, 216, 8, 4), A)
+t.check_frame(rt, ob, scenes.c1_like_scene(rt), rt.FrameParams.make(203, 151, 63, 4), A)
+sc = rt.Scene(scenes.c3_scene(rt, level=6, sky_size=128), device_id=0, accel=A)
 p = rt.FrameParams.make(2048, 1600, 8, 4)          # 13.1 M sample slots: above the two-sub-frame threshold
 img = sc.render(rt.CameraVectors.default(), p)
 crop = (960, 760, 1088, 824)
@@ -703,6 +704,8 @@ print('PARITY OK', sc.stats()['kernel_launches'])
     {"RT_SHADOW_STREAM": "0"},
     {"RT_EARLY_RESOLVE": "0"},
     {"RT_SORT_FROM": "1", "RT_SORT_TO": "8"},            # ray reordering between bounces
+    {"RT_WAVE": "1", "TEST_ACCEL": "3"},                 # warp-synchronous traversal of the 8-wide layout (rt_wave.cuh)
+    {"TEST_ACCEL": "3", "RT_SUBFRAMES": "1"},
 ], ids=lambda e: ",".join(f"{k}={v}" for k, v in e.items()))
 def test_switchable_paths_are_parity_green(gpu_rt, env):
     """Every run-time switch of the frame pipeline renders the same bits as the default path:

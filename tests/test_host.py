@@ -44,6 +44,7 @@ def test_struct_layouts_match_header(rt):
     assert C.sizeof(rt.MeshDesc) == 32 and C.sizeof(rt.InstanceDesc) == 56
     assert C.sizeof(rt.CameraVectors) == 48 and C.sizeof(rt.FrameParams) == 60 and C.sizeof(rt.Hit) == 20 and C.sizeof(rt.IpcHandle) == 64
     assert rt.HIT_DTYPE.itemsize == 20
+    assert C.sizeof(rt.Stats) == 152 and C.sizeof(rt.Material) == 44
 
 
 def test_no_device_means_error_not_fallback(rt):

@@ -398,6 +398,8 @@ def rt_lib():
         L.rt_render_frame.argtypes = [C.c_void_p, C.POINTER(CameraVectors), C.POINTER(FrameParams), C.c_void_p]
         L.rt_frame_output_bytes.restype = C.c_uint64
         L.rt_frame_output_bytes.argtypes = [C.POINTER(FrameParams)]
+        L.rt_host_buffer_pin.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+        L.rt_host_buffer_unpin.argtypes = [C.c_void_p]
         L.rt_frame_shard_pixels.restype = C.c_uint64
         L.rt_frame_shard_pixels.argtypes = [C.POINTER(FrameParams)]
         L.rt_assemble_shards.argtypes = [C.c_void_p, C.POINTER(FrameParams), C.c_void_p, C.c_void_p]
@@ -486,6 +488,17 @@ class Scene:
             out = np.zeros((p.height, p.width, 4), dt)
         _check(rt_lib().rt_render_frame(self._h, C.byref(camera), C.byref(p), out.ctypes.data))
         return out
+
+    def pin_host_buffer(self, array: np.ndarray):
+        """rt_host_buffer_pin: later host-output frames rendered into `array` (render_into with its address and
+        output_location = LOCATION_HOST) are stored by the resolve kernel directly, without a copy.  Keep the
+        array alive until unpin_host_buffer() / close()."""
+        self._pinned = array
+        _check(rt_lib().rt_host_buffer_pin(self._h, array.ctypes.data, array.nbytes))
+
+    def unpin_host_buffer(self):
+        _check(rt_lib().rt_host_buffer_unpin(self._h))
+        self._pinned = None
 
     def render_into(self, camera: CameraVectors, params: FrameParams, ptr: int):
         """Raw call: ptr is a host or device address per params.output_location."""

@@ -36,6 +36,11 @@ struct Scene {
   FramePipeline* pipe = nullptr;
   void* d_out = nullptr;
   size_t d_out_bytes = 0;
+  // caller's host frame buffer pinned by rt_host_buffer_pin: rt_render_frame(RT_LOCATION_HOST) into it stores the
+  // tiles straight from k_resolve (no device frame, no copy)
+  char* pin_host = nullptr;
+  char* pin_dev = nullptr;
+  size_t pin_bytes = 0;
   bool counting = false;
   rt_stats stats{};
 
@@ -130,6 +135,7 @@ static void destroy_scene(Scene* s) {
   cudaSetDevice(s->device);
   for (auto& b : s->blas) free_blas(b);
   cudaFree(s->d_blas); cudaFree(s->d_inst); cudaFree(s->d_mat); cudaFree(s->d_tlas); cudaFree(s->d_sky); cudaFree(s->d_out);
+  if (s->pin_host) cudaHostUnregister(s->pin_host);
   pipeline_destroy(s->pipe);
   delete s;
 }
@@ -340,9 +346,17 @@ static int render_common(Scene* s, const rt_camera* cam, const rt_frame_params* 
   rq.want_primary = d_primary != nullptr;
   rq.d_primary = d_primary;
   const size_t bytes = (size_t)rt_frame_output_bytes(p);
+  bool direct_host = false;
   if (out) {
     if (p->output_location == RT_LOCATION_DEVICE) {
       rq.d_out = out;
+    } else if (s->pin_host && rq.U.shard_count <= 1 && (char*)out >= s->pin_host &&
+               (char*)out + bytes <= s->pin_host + s->pin_bytes) {
+      // the caller pinned this buffer (rt_host_buffer_pin): k_resolve stores 128-byte runs of frame rows straight
+      // into it over PCIe, the finished sky tiles early, beside the traversal (same stores as rt_host_frame_*)
+      rq.d_out = s->pin_dev + ((char*)out - s->pin_host);
+      rq.U.in_frame = 1u;
+      direct_host = true;
     } else {
       if (bytes > s->d_out_bytes) {
         cudaFree(s->d_out);
@@ -356,7 +370,7 @@ static int render_common(Scene* s, const rt_camera* cam, const rt_frame_params* 
   }
   rc = pipeline_render(s->pipe, rq, s->stream, &s->stats, g_err);
   if (rc != RT_OK) return rc;
-  if (out && p->output_location == RT_LOCATION_HOST) {
+  if (out && p->output_location == RT_LOCATION_HOST && !direct_host) {
     RT_CUDA_TRY(cudaMemcpyAsync(out, s->d_out, bytes, cudaMemcpyDeviceToHost, s->stream), g_err);
     RT_CUDA_TRY(cudaStreamSynchronize(s->stream), g_err);
   }
@@ -367,6 +381,39 @@ int rt_render_frame(void* scene, const rt_camera* cam, const rt_frame_params* p,
   Scene* s = (Scene*)scene;
   if (!s || !rgba_out) return fail(RT_ERR_INVALID_ARGUMENT, "null scene or output");
   return render_common(s, cam, p, rgba_out, nullptr);
+}
+
+int rt_host_buffer_pin(void* scene, void* host, uint64_t bytes) {
+  Scene* s = (Scene*)scene;
+  if (!s || !host || bytes == 0) return fail(RT_ERR_INVALID_ARGUMENT, "null scene / buffer");
+  RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
+  if (s->pin_host) {
+    RT_CUDA_TRY(cudaStreamSynchronize(s->stream), g_err);
+    cudaHostUnregister(s->pin_host);
+    s->pin_host = s->pin_dev = nullptr;
+    s->pin_bytes = 0;
+  }
+  cudaError_t e = cudaHostRegister(host, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(RT_ERR_CUDA, std::string("cudaHostRegister: ") + cudaGetErrorString(e)); }
+  void* d = nullptr;
+  e = cudaHostGetDevicePointer(&d, host, 0);
+  if (e != cudaSuccess) { cudaHostUnregister(host); cudaGetLastError(); return fail(RT_ERR_CUDA, std::string("cudaHostGetDevicePointer: ") + cudaGetErrorString(e)); }
+  s->pin_host = (char*)host;
+  s->pin_dev = (char*)d;
+  s->pin_bytes = (size_t)bytes;
+  return RT_OK;
+}
+
+int rt_host_buffer_unpin(void* scene) {
+  Scene* s = (Scene*)scene;
+  if (!s) return fail(RT_ERR_INVALID_ARGUMENT, "null scene");
+  if (!s->pin_host) return RT_OK;
+  RT_CUDA_TRY(cudaSetDevice(s->device), g_err);
+  RT_CUDA_TRY(cudaStreamSynchronize(s->stream), g_err);
+  cudaHostUnregister(s->pin_host);
+  s->pin_host = s->pin_dev = nullptr;
+  s->pin_bytes = 0;
+  return RT_OK;
 }
 
 int rt_generate_normals(int device_id, float* vertices, uint32_t nv, const uint32_t* indices, uint32_t nt, double* device_ms) {

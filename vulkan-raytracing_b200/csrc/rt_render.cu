@@ -37,7 +37,6 @@ namespace rt { __device__ uint32_t g_trav_flags; }
 #endif
 
 #include "rt_internal.h"
-#include "rt_persist.cuh"
 #include "rt_wave.cuh"
 
 namespace rt {
@@ -222,8 +221,7 @@ __global__ void RT_TRACE_BOUNDS
     k_trace(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ rayO,
             const float4* __restrict__ rayD, uint4* __restrict__ hits, uint32_t* __restrict__ qMiss,
             uint32_t* __restrict__ qDiff, uint32_t* __restrict__ qSpec, rt_hit* __restrict__ primary,
-            unsigned long long* __restrict__ stats64, int refill_thresh, int tri_thresh,
-            const uint32_t* __restrict__ perm) {
+            unsigned long long* __restrict__ stats64, const uint32_t* __restrict__ perm) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
   uint2 stack_loc[STACK_LOCAL];
   HybridStack st;
@@ -231,13 +229,6 @@ __global__ void RT_TRACE_BOUNDS
   st.loc = stack_loc;
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NRAY];
-#ifdef RT_WITH_PERSIST
-  if (ACCEL == ACCEL_WIDE && refill_thresh > 0) {  // RT_REFILL=0: run-to-completion loop
-    TraceSource src{rayO, rayD};
-    TraceSink sink{scene, U, cnt, rayO, hits, qMiss, qDiff, qSpec, primary};
-    trace_wide_persistent<false, COUNT>(scene, n, &cnt[C_WTRACE], st, src, sink, tc, refill_thresh, tri_thresh);
-  } else
-#endif
   while (true) {
     // (32 rays per pull also at the end of the queue: shrinking the last batches to even out the
     // finishing times of the warps costs more in SIMD width than the shorter tail returns,
@@ -368,8 +359,7 @@ struct ShadowSink {
 template <int ACCEL, bool COUNT>
 __global__ void RT_TRACE_BOUNDS
     k_shadow(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
-             float4* __restrict__ sample, unsigned long long* __restrict__ stats64, int refill_thresh,
-             int tri_thresh) {
+             float4* __restrict__ sample, unsigned long long* __restrict__ stats64) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
   uint2 stack_loc[STACK_LOCAL];
   HybridStack st;
@@ -377,13 +367,6 @@ __global__ void RT_TRACE_BOUNDS
   st.loc = stack_loc;
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NSHADOW];
-#ifdef RT_WITH_PERSIST
-  if (ACCEL == ACCEL_WIDE && refill_thresh > 0) {  // RT_REFILL=0: run-to-completion loop
-    ShadowSource src{U, shadowQ};
-    ShadowSink sink{scene, U, shadowQ, sample};
-    trace_wide_persistent<true, COUNT>(scene, n, &cnt[C_WSHADOW], st, src, sink, tc, refill_thresh, tri_thresh);
-  } else
-#endif
   while (true) {
     uint32_t base = 0;
     if (lane_id() == 0) base = atomicAdd(&cnt[C_WSHADOW], 32u);
@@ -876,8 +859,6 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   const uint32_t accel = rq.scene.accel;
   const bool counting = rq.counting;
   // tuning knobs of the persistent traversal (defaults from the sweeps under profiles/)
-  static const int refill_t = getenv("RT_REFILL") ? atoi(getenv("RT_REFILL")) : 0;
-  static const int tri_t = getenv("RT_TRITHRESH") ? atoi(getenv("RT_TRITHRESH")) : 8;
   static const int sort_from = getenv("RT_SORT_FROM") ? atoi(getenv("RT_SORT_FROM")) : 1000;
   static const int sort_to = getenv("RT_SORT_TO") ? atoi(getenv("RT_SORT_TO")) : 1000;
   static const int sort_bits = std::min(30, std::max(8, getenv("RT_SORT_BITS") ? atoi(getenv("RT_SORT_BITS")) : 16));
@@ -983,7 +964,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     static int blocks = 0;                                                                                        \
     if (!blocks) blocks = persistent_blocks(k_trace<A, C>, TRACE_THREADS);                                        \
     k_trace<A, C><<<blocks, TRACE_THREADS, 0, cs>>>(rq.scene, U, cj, c.rayO[cur], c.rayD[cur], c.hits, c.qMiss,   \
-                                                    c.qDiff, c.qSpec, prim, p->stats64, refill_t, tri_t, perm);   \
+                                                    c.qDiff, c.qSpec, prim, p->stats64, perm);   \
   }
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 0], cs), err);
     if (wave) {
@@ -1006,7 +987,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   {                                                                                                       \
     static int blocks = 0;                                                                                \
     if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
-    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, refill_t, tri_t); \
+    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64); \
   }
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 2], sst), err);
     if (wave) {

@@ -65,6 +65,11 @@ enum {
 /* Ignore the normal slots of every mesh and fill them on the device with area-weighted
  * vertex normals (rt_generate_normals) before the build: for meshes whose file has no vn. */
 #define RT_FLAG_GENERATE_NORMALS 0x20u
+/* Sample the skybox through a hardware texture object (a 6-layer RGBA8 array, linear filter, clamp to edge:
+ * the VkSampler of main.cpp:2376-2412) instead of four texel loads and an FP32 lerp.  The texture unit
+ * filters with 8-bit fractional weights, so sky pixels may differ from the exact path by up to 1/255 (inside
+ * BASELINE.json's 2/255); off by default, where the image is bit-identical to the CPU oracle. */
+#define RT_FLAG_SKY_TEXTURE 0x40u
 
 /* One triangle mesh = one bottom-level acceleration structure.
  * Replaces createBLASGeometry/createBLAS/buildBLAS (main.cpp:305-536) and the

@@ -711,3 +711,56 @@ def test_switchable_paths_are_parity_green(gpu_rt, env):
     """Every run-time switch of the frame pipeline renders the same bits as the default path:
     the switches are read once per process, so each setting runs in its own interpreter."""
     assert "PARITY OK" in run_gpu_python(PARITY_SNIPPET, env)
+
+
+def test_repeated_large_frames_are_bit_identical(gpu_rt):
+    """compute-sanitizer is closed on this pool (profiles/r02_sanitizer.txt), so the race check of the multi-stream
+    frame (two sub-frames, shadow rays on their own streams, high-priority early resolve, cross-stream events) is
+    empirical: a frame above the two-sub-frame threshold rendered ten times, with device work of another stream
+    interleaved, must give the same bits every time - every sample slot is written by exactly one path, so any
+    ordering bug between the streams shows up as a changed pixel."""
+    import hashlib, torch
+    rt = gpu_rt
+    sc = rt.Scene(scenes.c3_scene(rt, level=6, sky_size=128), device_id=0)
+    cam = rt.CameraVectors.default()
+    p = rt.FrameParams.make(2048, 1600, 8, 4, output_location=rt.LOCATION_DEVICE)
+    out = torch.zeros((1600, 2048, 4), dtype=torch.uint8, device="cuda:0")
+    noise = torch.zeros(64 << 20, dtype=torch.uint8, device="cuda:0")
+    side = torch.cuda.Stream()
+    hashes = set()
+    for i in range(10):
+        out.zero_()
+        torch.cuda.synchronize()
+        with torch.cuda.stream(side):      # unrelated work competing for SMs and copy engines, different each time
+            for _ in range(i % 4):
+                noise.add_(1)
+        sc.render_into(cam, p, out.data_ptr())
+        torch.cuda.synchronize()
+        hashes.add(hashlib.sha256(out.cpu().numpy().tobytes()).hexdigest())
+        assert sc.stats()["stack_overflow"] == 0
+    assert len(hashes) == 1
+    sc.close()
+
+
+def test_sky_texture_object_within_tolerance(gpu_rt, ob):
+    """RT_FLAG_SKY_TEXTURE (north_star (3); the VkSampler of main.cpp:2376-2412 as a CUDA texture object): the hardware
+    filter uses 8-bit weights, so the frame may differ from the exact path - by at most 2/255 (BASELINE.json), PSNR >= 45 dB,
+    and the traced rays are the same."""
+    rt = gpu_rt
+    cam = rt.CameraVectors.default()
+    for inputs, p in ((scenes.c2_scene(rt, 256), rt.FrameParams.make(480, 270, 4, 4)),
+                      (scenes.c1_scene(rt), rt.FrameParams.make(400, 300, 63, 4)),
+                      (scenes.smoke_scene(rt), rt.FrameParams.make(160, 120, 6, 4))):
+        exact = rt.Scene(inputs, device_id=0)
+        a = exact.render(cam, p)
+        sa = exact.stats()
+        exact.close()
+        tex = rt.Scene(inputs, device_id=0, flags=rt.FLAG_SKY_TEXTURE)
+        b = tex.render(cam, p)
+        sb = tex.stats()
+        tex.close()
+        d = np.abs(a.astype(np.int32) - b.astype(np.int32))
+        assert d.max() <= 2 and psnr(a, b) >= 45.0, (d.max(), psnr(a, b))
+        assert np.array_equal(a, ob.OracleScene(inputs).render(cam, p)["rgba8"])
+        for k in ("rays_primary", "rays_secondary", "rays_shadow", "n_miss", "n_hit"):
+            assert sa[k] == sb[k]

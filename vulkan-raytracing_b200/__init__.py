@@ -34,6 +34,7 @@ SHARD_COMPACT, SHARD_IN_FRAME = 0, 1
 ACCEL_DEFAULT, ACCEL_BVH2, ACCEL_BRUTE, ACCEL_WIDE8 = 0, 1, 2, 3
 FLAG_NO_REFINE = 0x10
 FLAG_GENERATE_NORMALS = 0x20
+FLAG_SKY_TEXTURE = 0x40
 MISS = 0xFFFFFFFF
 
 

@@ -32,6 +32,8 @@ struct Scene {
   float4* d_tlas = nullptr;
   size_t d_tlas_cap = 0;
   uint8_t* d_sky = nullptr;
+  cudaArray_t sky_array = nullptr;        // RT_FLAG_SKY_TEXTURE: 6-layer RGBA8 array + texture object
+  cudaTextureObject_t sky_tex = 0;
   uint32_t sky_w = 0, sky_h = 0;
   FramePipeline* pipe = nullptr;
   void* d_out = nullptr;
@@ -52,6 +54,7 @@ struct Scene {
     s.n_inst = (uint32_t)inst.size();
     s.accel = accel;
     s.sky = d_sky;
+    s.sky_tex = (unsigned long long)sky_tex;
     s.sky_w = sky_w;
     s.sky_h = sky_h;
     for (int k = 0; k < 3; k++) {
@@ -136,6 +139,8 @@ static void destroy_scene(Scene* s) {
   for (auto& b : s->blas) free_blas(b);
   cudaFree(s->d_blas); cudaFree(s->d_inst); cudaFree(s->d_mat); cudaFree(s->d_tlas); cudaFree(s->d_sky); cudaFree(s->d_out);
   if (s->pin_host) cudaHostUnregister(s->pin_host);
+  if (s->sky_tex) cudaDestroyTextureObject(s->sky_tex);
+  if (s->sky_array) cudaFreeArray(s->sky_array);
   pipeline_destroy(s->pipe);
   delete s;
 }
@@ -274,6 +279,25 @@ int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
     const size_t bytes = (size_t)6 * d->sky_w * d->sky_h * 4;
     RT_CUDA_TRY(cudaMalloc(&s->d_sky, bytes), g_err);
     RT_CUDA_TRY(cudaMemcpy(s->d_sky, d->skybox_rgba8, bytes, cudaMemcpyHostToDevice), g_err);
+    if (d->flags & RT_FLAG_SKY_TEXTURE) {   // the sampler of main.cpp:2376-2412 as a CUDA texture object
+      const cudaChannelFormatDesc ch = cudaCreateChannelDesc<uchar4>();
+      RT_CUDA_TRY(cudaMalloc3DArray(&s->sky_array, &ch, make_cudaExtent(d->sky_w, d->sky_h, 6), cudaArrayLayered), g_err);
+      cudaMemcpy3DParms cp = {};
+      cp.srcPtr = make_cudaPitchedPtr((void*)d->skybox_rgba8, (size_t)d->sky_w * 4, d->sky_w, d->sky_h);
+      cp.dstArray = s->sky_array;
+      cp.extent = make_cudaExtent(d->sky_w, d->sky_h, 6);
+      cp.kind = cudaMemcpyHostToDevice;
+      RT_CUDA_TRY(cudaMemcpy3D(&cp), g_err);
+      cudaResourceDesc rd = {};
+      rd.resType = cudaResourceTypeArray;
+      rd.res.array.array = s->sky_array;
+      cudaTextureDesc td = {};
+      td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;   // CLAMP_TO_EDGE per face (main.cpp:2395-2399)
+      td.filterMode = cudaFilterModeLinear;                           // VK_FILTER_LINEAR (main.cpp:2393-2394)
+      td.readMode = cudaReadModeNormalizedFloat;                      // R8G8B8A8_UNORM (main.cpp:2124)
+      td.normalizedCoords = 0;
+      RT_CUDA_TRY(cudaCreateTextureObject(&s->sky_tex, &rd, &td, nullptr), g_err);
+    }
     s->sky_w = d->sky_w;
     s->sky_h = d->sky_h;
   }

@@ -101,6 +101,12 @@ RT_HD f3 sky_sample(const SceneDev& s, f3 r) {
     if (r.x >= 0.0f) { face = 0; sc = -r.z; tc = -r.y; } else { face = 1; sc = r.z; tc = -r.y; }
   }
   const float fs = fmaf(0.5f, sc / ma, 0.5f), ft = fmaf(0.5f, tc / ma, 0.5f);
+#if defined(__CUDA_ARCH__)
+  if (s.sky_tex) {  // RT_FLAG_SKY_TEXTURE: the texture unit does the four fetches, the clamp and the filter
+    const float4 c = tex2DLayered<float4>((cudaTextureObject_t)s.sky_tex, fs * (float)s.sky_w, ft * (float)s.sky_h, face);
+    return mk3(c.x, c.y, c.z);
+  }
+#endif
   const float u = fmaf(fs, (float)s.sky_w, -0.5f), v = fmaf(ft, (float)s.sky_h, -0.5f);
   const float fu = floorf(u), fv = floorf(v);
   const float wx = u - fu, wy = v - fv;

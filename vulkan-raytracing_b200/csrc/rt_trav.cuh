@@ -68,6 +68,7 @@ struct SceneDev {
   float shi[3];
   const float4* tlas;     // binary tree over the instance boxes (rt_tlas.hpp); null for small scenes
   uint32_t n_tlas;
+  unsigned long long sky_tex;  // cudaTextureObject_t over the 6-layer sky array (RT_FLAG_SKY_TEXTURE), else 0
 };
 
 struct HitRec {

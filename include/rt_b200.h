@@ -330,6 +330,24 @@ int rt_measure_fp32_tflops(int device_id, double* tflops_out);
 int rt_debug_sort_pairs(int device_id, uint64_t n, const uint64_t* keys_in,
                         const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out);
 
+/* --- allocation-free variant (no counterpart in the reference) ---------------- */
+/* This entry point has no counterpart in the reference; it was added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  It is the same one-sweep radix sort as above (stable, by the full 64-bit key), but on DEVICE pointers, in
+ * place, and it allocates nothing: the sort's scratch (ping-pong copies of keys and values, digit histograms,
+ * tile status words) is a fixed file-scope device array of 14.0 MiB sized for RT_SORT_NOALLOC_MAX_PAIRS pairs,
+ * which every GPU that loads the library holds until the process exits.
+ *   d_keys / d_vals: n keys / n values in device memory of `device_id`, sorted in place (the caller owns them);
+ *   n > RT_SORT_NOALLOC_MAX_PAIRS is refused with RT_ERR_UNSUPPORTED and a message in rt_last_error();
+ *   the work is enqueued on `stream` (cudaStream_t, NULL = default stream) and NOT waited for; no cudaMalloc,
+ *   cudaFree or other allocating call is made (the first call on a device looks up the array's address with
+ *   cudaGetSymbolAddress: make that first call outside a graph capture).
+ * Every call shares the one scratch array: calls that overlap on the GPU (different streams, or another thread or
+ * process context on the same library instance) race and give wrong results; calls ordered on one stream are fine.
+ * The array keeps the last call's contents; the sort clears the words that must start at zero itself. */
+#define RT_SORT_NOALLOC_MAX_PAIRS (1u << 20)
+int rt_sort_pairs_noalloc(int device_id, uint64_t n, uint64_t* d_keys, uint32_t* d_vals, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

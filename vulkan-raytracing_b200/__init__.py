@@ -35,6 +35,7 @@ ACCEL_DEFAULT, ACCEL_BVH2, ACCEL_BRUTE, ACCEL_WIDE8 = 0, 1, 2, 3
 FLAG_NO_REFINE = 0x10
 FLAG_GENERATE_NORMALS = 0x20
 FLAG_SKY_TEXTURE = 0x40
+SORT_NOALLOC_MAX_PAIRS = 1 << 20
 MISS = 0xFFFFFFFF
 
 
@@ -421,6 +422,7 @@ def rt_lib():
         L.rt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
         L.rt_measure_fp32_tflops.argtypes = [C.c_int, C.POINTER(C.c_double)]
         L.rt_debug_sort_pairs.argtypes = [C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.rt_sort_pairs_noalloc.argtypes = [C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
         _rt = L
     return _rt
 

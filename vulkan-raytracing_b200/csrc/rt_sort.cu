@@ -259,3 +259,67 @@ int sort_pairs_u32(uint32_t* keys, uint32_t* keys_alt, uint32_t* vals, uint32_t*
 int sort_launches(int key_bits) { return 3 + ((((key_bits + 7) / 8) + 1) & ~1); }
 
 }  // namespace rt
+
+// ---- rt_sort_pairs_noalloc: the same sort for callers that must not allocate ---------------------------
+// (no counterpart in the reference, see include/rt_b200.h)
+// The sort's scratch - the ping-pong copies of the keys and values and the histogram / tile-status words -
+// lives in ONE file-scope device array sized for RT_SORT_NOALLOC_MAX_PAIRS pairs instead of cudaMalloc'd
+// buffers.  Every GPU that loads the library holds the array until the process exits; every call shares it.
+namespace rt {
+
+constexpr uint64_t NOALLOC_MAX = RT_SORT_NOALLOC_MAX_PAIRS;
+constexpr size_t NOALLOC_KEYS_BYTES = (size_t)NOALLOC_MAX * sizeof(uint64_t);          // keys_alt
+constexpr size_t NOALLOC_VALS_BYTES = (size_t)NOALLOC_MAX * sizeof(uint32_t);          // vals_alt
+constexpr size_t NOALLOC_HIST_WORDS =
+    (size_t)OS_MAX_PASSES * 256 + 16 + (size_t)OS_MAX_PASSES * 256 * ((NOALLOC_MAX + OS_TILE - 1) / OS_TILE);   // = sort_hist_words(max)
+constexpr size_t NOALLOC_BYTES = NOALLOC_KEYS_BYTES + NOALLOC_VALS_BYTES + NOALLOC_HIST_WORDS * sizeof(uint32_t);
+static_assert(NOALLOC_KEYS_BYTES % 256 == 0 && NOALLOC_VALS_BYTES % 256 == 0, "pieces of the scratch array stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_sort_scratch[NOALLOC_BYTES];   // 14.0 MiB for 2^20 pairs
+
+// In host code `g_sort_scratch` is only a stand-in for the symbol, not a device address: the address is asked
+// for once per device, with that device current, and kept here.
+static const int NOALLOC_MAX_DEVICES = 64;
+static unsigned char* g_sort_scratch_addr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+extern thread_local std::string g_err;   // rt_api.cu: message behind rt_last_error()
+
+}  // namespace rt
+
+extern "C" int rt_sort_pairs_noalloc(int device_id, uint64_t n, uint64_t* d_keys, uint32_t* d_vals, void* stream) {
+  using namespace rt;
+  if (n > NOALLOC_MAX) {
+    g_err = "rt_sort_pairs_noalloc: " + std::to_string(n) + " pairs exceed the fixed scratch of RT_SORT_NOALLOC_MAX_PAIRS = " +
+            std::to_string(NOALLOC_MAX) + " pairs (use the allocating sort for larger inputs)";
+    return RT_ERR_UNSUPPORTED;
+  }
+  if (n && (!d_keys || !d_vals)) { g_err = "rt_sort_pairs_noalloc: null device pointer"; return RT_ERR_INVALID_ARGUMENT; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+    cudaGetLastError();
+    g_err = "no CUDA device: librt_b200 has no CPU fallback";
+    return RT_ERR_NO_DEVICE;
+  }
+  if (device_id < 0) device_id = 0;
+  if (device_id >= ndev || device_id >= NOALLOC_MAX_DEVICES) { g_err = "rt_sort_pairs_noalloc: bad device_id"; return RT_ERR_INVALID_ARGUMENT; }
+  if (n == 0) return RT_OK;
+  RT_CUDA_TRY(cudaSetDevice(device_id), g_err);
+  if (!g_sort_scratch_addr[device_id]) {   // set-up, once per device, that device current
+    unsigned char* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_sort_scratch);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      g_err = std::string("rt_sort_pairs_noalloc: cudaGetSymbolAddress(g_sort_scratch): ") + cudaGetErrorString(e);
+      return RT_ERR_CUDA;
+    }
+    g_sort_scratch_addr[device_id] = p;
+  }
+  unsigned char* base = g_sort_scratch_addr[device_id];
+  uint64_t* keys_alt = (uint64_t*)base;
+  uint32_t* vals_alt = (uint32_t*)(base + NOALLOC_KEYS_BYTES);
+  uint32_t* hist = (uint32_t*)(base + NOALLOC_KEYS_BYTES + NOALLOC_VALS_BYTES);
+  // sort_pairs clears the histogram, control and tile-status words it uses at the start of every call (the array
+  // keeps the last call's contents); keys_alt / vals_alt are fully written before they are read.  64 key bits =
+  // 8 passes, an even number: the result lands in d_keys / d_vals.  Nothing here allocates or synchronises.
+  return sort_pairs(d_keys, keys_alt, d_vals, vals_alt, n, 64, hist, (cudaStream_t)stream, g_err);
+}

@@ -56,8 +56,10 @@ enum {
                              ordered traversal                                            */
   RT_ACCEL_BRUTE = 2,     /* no hierarchy: every ray tests every triangle (tiny scenes
                              only; parity cross-check)                                    */
-  RT_ACCEL_WIDE8 = 3      /* compressed 8-wide nodes (80 B, 8-bit quantised child boxes,
+  RT_ACCEL_WIDE8 = 3,     /* compressed 8-wide nodes (80 B, 8-bit quantised child boxes,
                              Ylitie et al. 2017): least memory traffic per ray            */
+  RT_ACCEL_WIDE4 = 4      /* 4-wide nodes, full FP32 child boxes, 128 B = one cache line: half the
+                             dependent node fetches per ray of the binary layout, no decode     */
 };
 #define RT_FLAG_ACCEL_MASK 0xFu
 /* Skip the SAH treelet refinement of the Karras tree (faster build, slower rays). */

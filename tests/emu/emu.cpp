@@ -140,6 +140,21 @@ void build(EmuBlas& b, uint32_t accel) {
       b.nodes = end;
       b.wide.resize(5 * (size_t)end);
       b.dev.nodes = (const float4*)b.wide.data();
+    } else if (accel == ACCEL_BVH4 && N > 1) {
+      b.bvh2.resize(8 * (size_t)std::max<uint32_t>(N - 1, 1));   // (the float4 array is shared with the binary layout)
+      work[0] = 0; counters[0] = 1; counters[1] = 0;
+      uint32_t begin = 0, end = 1;
+      while (begin < end) {
+        for (uint32_t w = begin; w < end; w++) collapse4_node(a, w, b.bvh2.data());
+        begin = end; end = counters[0];
+      }
+      for (uint32_t i = 0; i < N; i++) emit_tri(a, i, vals[i], b.tris.data());
+      b.nodes = end;
+      b.bvh2.resize(8 * (size_t)end);
+      b.dev.nodes = b.bvh2.data();
+    } else if (accel == ACCEL_BVH4) {
+      for (uint32_t i = 0; i < N; i++) emit_tri(a, i, vals[i], b.tris.data());
+      b.nodes = 0;
     } else {
       b.bvh2.resize(4 * (size_t)std::max<uint32_t>(N - 1, 1));
       for (uint32_t i = 0; i < N; i++) {
@@ -183,7 +198,8 @@ int emu_scene_create(const rt_scene_desc* d, void** out) {
   auto s = std::make_unique<EmuScene>();
   {  // same API flavour -> traversal id mapping as rt_scene_build()
     const uint32_t f = d->flags & RT_FLAG_ACCEL_MASK;
-    s->accel = f == RT_ACCEL_WIDE8 ? (uint32_t)ACCEL_WIDE : (f == RT_ACCEL_BRUTE ? (uint32_t)ACCEL_BRUTE : (uint32_t)ACCEL_BVH2);
+    s->accel = f == RT_ACCEL_WIDE8 ? (uint32_t)ACCEL_WIDE : f == RT_ACCEL_WIDE4 ? (uint32_t)ACCEL_BVH4
+               : (f == RT_ACCEL_BRUTE ? (uint32_t)ACCEL_BRUTE : (uint32_t)ACCEL_BVH2);
   }
   s->blas.resize(d->n_meshes);
   for (uint32_t i = 0; i < d->n_meshes; i++) {

@@ -24,7 +24,7 @@ def compare(rt, ob, emu, inputs, params, accel, cam=None, materials=None):
     return a["counts"]
 
 
-@pytest.mark.parametrize("accel", [0, 2, 3])
+@pytest.mark.parametrize("accel", [0, 2, 3, 4])
 def test_smoke_scene_bit_exact(rt, ob, emu, accel):
     compare(rt, ob, emu, scenes.smoke_scene(rt), rt.FrameParams.make(96, 72, 6, 3), accel)
 
@@ -74,7 +74,7 @@ def test_rotated_instances_and_camera(rt, ob, emu):
     compare(rt, ob, emu, inputs, rt.FrameParams.make(90, 60, 5, 2), 0, cam.vectors())
 
 
-@pytest.mark.parametrize("accel", [0, 3])
+@pytest.mark.parametrize("accel", [0, 3, 4])
 def test_many_instances_use_the_top_level_tree(rt, ob, emu, accel):
     compare(rt, ob, emu, scenes.instanced_grid_scene(rt), rt.FrameParams.make(120, 80, 5, 2), accel)
 
@@ -83,7 +83,7 @@ def test_tiny_and_degenerate_meshes(rt, ob, emu):
     cv, ci = scenes.unit_cube()
     one = (np.array([[-3, -3, 0, 0, 0, 1], [3, -3, 0, 0, 0, 1], [0, 3, 0, 0, 0, 1]], np.float32),
            np.array([[0, 1, 2]], np.uint32))
-    for accel in (0, 2, 3):
+    for accel in (0, 2, 3, 4):
         compare(rt, ob, emu, rt.SceneInputs([one], [(0, 0, rt.IDENTITY34)], None), rt.FrameParams.make(40, 30, 0, 1), accel)
     two = (cv, ci[:2])
     dup = (np.concatenate([cv, cv[:3]]), np.concatenate([ci, ci[:4], np.array([[0, 0, 1], [2, 2, 2]], np.uint32)]))
@@ -91,7 +91,7 @@ def test_tiny_and_degenerate_meshes(rt, ob, emu):
     inputs = rt.SceneInputs([two, dup, empty], [(0, 1, rt.translation34(-3, 0, 0)), (1, 2, rt.IDENTITY34),
                                                 (2, 0, rt.IDENTITY34), (1, 7, rt.translation34(3, 0, 2))],
                             scenes.sea_sky_64())
-    for accel in (0, 3):
+    for accel in (0, 3, 4):
         compare(rt, ob, emu, inputs, rt.FrameParams.make(80, 60, 4, 2), accel)
 
 

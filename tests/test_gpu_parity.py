@@ -45,7 +45,7 @@ def check_frame(rt, ob, inputs, params, accel=0, cam=None, exact=True):
     return st
 
 
-@pytest.mark.parametrize("accel", [0, 2, 3])
+@pytest.mark.parametrize("accel", [0, 2, 3, 4])
 def test_smoke_scene_all_accels(gpu_rt, ob, accel):
     check_frame(gpu_rt, ob, scenes.smoke_scene(gpu_rt), gpu_rt.FrameParams.make(160, 120, 6, 4), accel)
 
@@ -131,7 +131,7 @@ def test_set_transforms_matches_rebuild(gpu_rt, ob):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("accel", [0, 3])
+@pytest.mark.parametrize("accel", [0, 3, 4])
 def test_instanced_grid_top_level_tree(gpu_rt, ob, accel):
     """13 instances (> RT_TLAS_MIN_INSTANCES): rays walk the top-level tree; also after a transform update."""
     rt = gpu_rt
@@ -191,7 +191,7 @@ def test_trace_rays_closest_and_any(gpu_rt, ob):
     sc.close()
 
 
-@pytest.mark.parametrize("accel", [0, 3])
+@pytest.mark.parametrize("accel", [0, 3, 4])
 def test_axis_parallel_and_far_rays(gpu_rt, ob, accel):
     """Box culling must stay conservative where the slab arithmetic degenerates: directions with
     exactly-zero components (1/d clamped), origins lying on box planes, origins far from the
@@ -706,6 +706,7 @@ print('PARITY OK', sc.stats()['kernel_launches'])
     {"RT_SORT_FROM": "1", "RT_SORT_TO": "8"},            # ray reordering between bounces
     {"RT_WAVE": "1", "TEST_ACCEL": "3"},                 # warp-synchronous traversal of the 8-wide layout (rt_wave.cuh)
     {"TEST_ACCEL": "3", "RT_SUBFRAMES": "1"},
+    {"TEST_ACCEL": "4"},                                 # 4-wide full-precision nodes (RT_ACCEL_WIDE4)
 ], ids=lambda e: ",".join(f"{k}={v}" for k, v in e.items()))
 def test_switchable_paths_are_parity_green(gpu_rt, env):
     """Every run-time switch of the frame pipeline renders the same bits as the default path:

@@ -31,7 +31,7 @@ TYPE_DIFFUSE, TYPE_MIRROR, TYPE_REFRACTIVE = 0, 1, 2
 FORMAT_RGBA8, FORMAT_RGBA32F = 0, 1
 LOCATION_HOST, LOCATION_DEVICE = 0, 1
 SHARD_COMPACT, SHARD_IN_FRAME = 0, 1
-ACCEL_DEFAULT, ACCEL_BVH2, ACCEL_BRUTE, ACCEL_WIDE8 = 0, 1, 2, 3
+ACCEL_DEFAULT, ACCEL_BVH2, ACCEL_BRUTE, ACCEL_WIDE8, ACCEL_WIDE4 = 0, 1, 2, 3, 4
 FLAG_NO_REFINE = 0x10
 FLAG_GENERATE_NORMALS = 0x20
 FLAG_SKY_TEXTURE = 0x40

@@ -201,9 +201,10 @@ int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
   *out_scene = nullptr;
   if (d->n_meshes == 0 || !d->meshes || (d->n_instances && !d->instances)) return fail(RT_ERR_INVALID_ARGUMENT, "empty scene");
   const uint32_t accel_flag = d->flags & RT_FLAG_ACCEL_MASK;
-  if (accel_flag > RT_ACCEL_WIDE8) return fail(RT_ERR_INVALID_ARGUMENT, "unknown accel flag");
+  if (accel_flag > RT_ACCEL_WIDE4) return fail(RT_ERR_INVALID_ARGUMENT, "unknown accel flag");
   // API flavour -> internal traversal id (template parameter of the kernels)
   const uint32_t accel = accel_flag == RT_ACCEL_WIDE8 ? (uint32_t)ACCEL_WIDE
+                         : accel_flag == RT_ACCEL_WIDE4 ? (uint32_t)ACCEL_BVH4
                          : accel_flag == RT_ACCEL_BRUTE ? (uint32_t)ACCEL_BRUTE : (uint32_t)ACCEL_BVH2;
   const bool refine = (d->flags & RT_FLAG_NO_REFINE) == 0;
   for (uint32_t i = 0; i < d->n_meshes; i++) {
@@ -259,7 +260,7 @@ int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
     s->stats.bvh_bytes += s->blas[i].bytes;
     s->stats.max_tree_depth = std::max(s->stats.max_tree_depth, s->blas[i].depth);
   }
-  s->stats.node_bytes = accel == ACCEL_WIDE ? 80 : (accel == ACCEL_BVH2 ? 64 : 0);
+  s->stats.node_bytes = accel == ACCEL_WIDE ? 80 : (accel == ACCEL_BVH2 ? 64 : (accel == ACCEL_BVH4 ? 128 : 0));
   s->stats.tri_bytes = 48;
   RT_CUDA_TRY(cudaMalloc(&s->d_blas, hb.size() * sizeof(BlasDev)), g_err);
   RT_CUDA_TRY(cudaMemcpy(s->d_blas, hb.data(), hb.size() * sizeof(BlasDev), cudaMemcpyHostToDevice), g_err);

@@ -150,6 +150,17 @@ __global__ void __launch_bounds__(256) k_emit_bvh2(BuildArrays a, float4* nodes,
   }
 }
 
+__global__ void __launch_bounds__(128) k_collapse4(BuildArrays a, float4* out, uint32_t begin, uint32_t end) {
+  for (uint32_t w = begin + blockIdx.x * blockDim.x + threadIdx.x; w < end; w += gridDim.x * blockDim.x)
+    collapse4_node(a, w, out);
+}
+
+// leaf triangles in sorted (Morton) order, as the binary layout has them
+__global__ void __launch_bounds__(256) k_emit_sorted_tris(BuildArrays a, float4* tris) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.ntri; i += gridDim.x * blockDim.x)
+    emit_tri(a, i, a.vals[i], tris);
+}
+
 // depth of the final binary tree -> bounds[12] (one parent walk per leaf, warp-reduced)
 __global__ void __launch_bounds__(256) k_tree_depth(BuildArrays a) {
   uint32_t d = 0;
@@ -220,10 +231,11 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
   b.bytes = 0;
   if (ntri == 0) return RT_OK;
   const size_t N = ntri;
+  uint32_t wide_levels = 0;   // ACCEL_BVH4: levels of the 4-wide tree
   TempAlloc tmp;
   {  // bytes per triangle of every array requested below (+ the 8-wide staging), plus slack for alignment
     size_t per_tri = 32 + 16;
-    if (accel != ACCEL_BRUTE) per_tri += 16 + 8 + 8 + 12 + 4 + 64 + 4 + (refine ? 8 + 8 : 0) + (accel == ACCEL_WIDE ? 80 + 4 : 0);
+    if (accel != ACCEL_BRUTE) per_tri += 16 + 8 + 8 + 12 + 4 + 64 + 4 + (refine ? 8 + 8 : 0) + (accel == ACCEL_WIDE ? 80 + 4 : 0) + (accel == ACCEL_BVH4 ? 128 + 4 : 0);
     tmp.reserve(N * per_tri + sort_hist_words(N) * sizeof(uint32_t) + (1u << 20));
   }
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -341,6 +353,33 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
     RT_CUDA_TRY(cudaMalloc(&b.d_nodes, (size_t)end * 80), err);
     RT_CUDA_TRY(cudaMemcpyAsync(b.d_nodes, wide_tmp, (size_t)end * 80, cudaMemcpyDeviceToDevice, stream), err);
     b.bytes = (uint64_t)end * 80 + N * 48;
+  } else if (accel == ACCEL_BVH4 && ntri > 1) {
+    // top-down, one launch per level of the 4-wide tree (each level queues the next: one look at the count per level)
+    float4* wide_tmp = nullptr;
+    RT_CUDA_TRY(tmp.get(&wide_tmp, 8 * std::max<size_t>(N - 1, 1)), err);   // at most one wide node per binary node
+    RT_CUDA_TRY(tmp.get(&a.work, N), err);
+    RT_CUDA_TRY(tmp.get(&a.counters, 4), err);
+    k_set_root<<<1, 1, 0, stream>>>(a.work, a.counters);
+    uint32_t begin = 0, end = 1;
+    wide_levels = 0;
+    while (begin < end) {
+      k_collapse4<<<grid_for(end - begin, 128), 128, 0, stream>>>(a, wide_tmp, begin, end);
+      uint32_t counters[2];
+      RT_CUDA_TRY(cudaMemcpyAsync(counters, a.counters, sizeof counters, cudaMemcpyDeviceToHost, stream), err);
+      RT_CUDA_TRY(cudaStreamSynchronize(stream), err);
+      begin = end;
+      end = counters[0];
+      wide_levels++;
+      if (end > N) { err = "4-wide node overflow"; return RT_ERR_CUDA; }
+    }
+    b.node_count = end;
+    RT_CUDA_TRY(cudaMalloc(&b.d_nodes, (size_t)end * 128), err);
+    RT_CUDA_TRY(cudaMemcpyAsync(b.d_nodes, wide_tmp, (size_t)end * 128, cudaMemcpyDeviceToDevice, stream), err);
+    k_emit_sorted_tris<<<grid_for(N, 256), 256, 0, stream>>>(a, (float4*)b.d_tris);
+    b.bytes = (uint64_t)end * 128 + N * 48;
+  } else if (accel == ACCEL_BVH4) {
+    k_emit_sorted_tris<<<grid_for(N, 256), 256, 0, stream>>>(a, (float4*)b.d_tris);
+    b.bytes = N * 48;
   } else if (accel == ACCEL_BVH2) {
     k_emit_bvh2<<<grid_for(N, 256), 256, 0, stream>>>(a, (float4*)b.d_nodes, (float4*)b.d_tris);
     b.node_count = N - 1;
@@ -385,6 +424,10 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
   static const uint32_t depth_env = getenv("RT_DEPTH_LIMIT") ? (uint32_t)atoi(getenv("RT_DEPTH_LIMIT")) : 0u;
   uint32_t limit = accel == ACCEL_WIDE ? RT_MAX_TREE_DEPTH / 2 : RT_MAX_TREE_DEPTH;
   if (depth_env) limit = std::min(limit, depth_env);
+  if (accel == ACCEL_BVH4) {   // up to three postponed children per level of the 4-wide tree
+    b.depth = wide_levels;
+    limit = limit / 3;
+  }
   if (accel != ACCEL_BRUTE && b.depth > limit) {
     err = "mesh not supported: its acceleration structure is " + std::to_string(b.depth) + " levels deep, the traversal stack holds " +
           std::to_string(limit);

@@ -543,6 +543,71 @@ RT_HD void collapse_node(const BuildArrays& a, uint32_t w) {
   o[4] = make_uint4(qhy[0], qhy[1], qhz[0], qhz[1]);
 }
 
+// ---- 4-wide nodes (ACCEL_BVH4) ------------------------------------------------------------------------
+// 128-byte node = 8 x float4, child boxes in full FP32 and SoA order (no decode in the traversal):
+//   q0 = lo.x[0..3]  q1 = lo.y[0..3]  q2 = lo.z[0..3]  q3 = hi.x[0..3]  q4 = hi.y[0..3]  q5 = hi.z[0..3]
+//   q6 = child[0..3] as int bits: >= 0 wide node index, < 0 leaf triangle ~slot (sorted position, the BVH2 leaf
+//        array), BVH4_EMPTY = no child          q7 = padding (the node is one 128-byte line)
+// Built from the refined binary tree top-down: wide node w stands for binary node work[w]; its children are
+// that node's two children with the largest-area inner child opened until there are four (so the halves of big
+// boxes become siblings and a ray that misses one skips it without a fetch).  Inner children are queued as the
+// next wide nodes: one dependent fetch per TWO binary levels is what the layout is for.
+static const int BVH4_EMPTY = (int)0x80000000;
+RT_HD void collapse4_node(const BuildArrays& a, uint32_t w, float4* out) {
+  const int n = (int)a.ntri;
+  const int root = (int)a.work[w];
+  int ch[4];
+  int nch = 0;
+  ch[nch++] = a.left[root];
+  ch[nch++] = a.right[root];
+  while (nch < 4) {
+    int best = -1;
+    float barea = -1.0f;
+    for (int c = 0; c < nch; c++) {
+      const int id = ch[c];
+      if (id >= n - 1) continue;   // a triangle
+      const float ar = half_area(a.node_lo[id], a.node_hi[id]);
+      if (ar > barea) { barea = ar; best = c; }
+    }
+    if (best < 0) break;
+    const int id = ch[best];
+    ch[best] = a.left[id];
+    ch[nch++] = a.right[id];
+  }
+  uint32_t n_inner = 0;
+  for (int c = 0; c < nch; c++) n_inner += ch[c] < n - 1 ? 1u : 0u;
+  const uint32_t child_base = n_inner ? RT_ATOMIC_ADD(&a.counters[0], n_inner) : 0u;
+  float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];
+  uint32_t ref[4];
+  uint32_t rank = 0;
+  for (int c = 0; c < 4; c++) {
+    if (c >= nch) {
+      lox[c] = loy[c] = loz[c] = 0.0f; hix[c] = hiy[c] = hiz[c] = 0.0f;
+      ref[c] = (uint32_t)BVH4_EMPTY;
+      continue;
+    }
+    const int id = ch[c];
+    const float4 lo = a.node_lo[id], hi = a.node_hi[id];
+    lox[c] = lo.x; loy[c] = lo.y; loz[c] = lo.z; hix[c] = hi.x; hiy[c] = hi.y; hiz[c] = hi.z;
+    if (id >= n - 1) {
+      ref[c] = (uint32_t)~(id - (n - 1));
+    } else {
+      a.work[child_base + rank] = (uint32_t)id;
+      ref[c] = child_base + rank;
+      rank++;
+    }
+  }
+  float4* o = out + 8 * (size_t)w;
+  o[0] = make_float4(lox[0], lox[1], lox[2], lox[3]);
+  o[1] = make_float4(loy[0], loy[1], loy[2], loy[3]);
+  o[2] = make_float4(loz[0], loz[1], loz[2], loz[3]);
+  o[3] = make_float4(hix[0], hix[1], hix[2], hix[3]);
+  o[4] = make_float4(hiy[0], hiy[1], hiy[2], hiy[3]);
+  o[5] = make_float4(hiz[0], hiz[1], hiz[2], hiz[3]);
+  o[6] = make_float4(u2f(ref[0]), u2f(ref[1]), u2f(ref[2]), u2f(ref[3]));
+  o[7] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
 // Number of binary nodes above leaf j (sorted position) in the final tree: the stack an ordered
 // traversal needs on the way to that leaf is at most this.  Walks the parent links (valid after
 // the treelet pass, which rewrites them with the children).  The bound on the walk only guards

@@ -821,6 +821,7 @@ static int stride_blocks(uint64_t n, int threads) {
   do {                                                                    \
     if ((accel) == ACCEL_WIDE) { if (counting) { CALL(ACCEL_WIDE, true); } else { CALL(ACCEL_WIDE, false); } }        \
     else if ((accel) == ACCEL_BVH2) { if (counting) { CALL(ACCEL_BVH2, true); } else { CALL(ACCEL_BVH2, false); } }   \
+    else if ((accel) == ACCEL_BVH4) { if (counting) { CALL(ACCEL_BVH4, true); } else { CALL(ACCEL_BVH4, false); } }   \
     else { if (counting) { CALL(ACCEL_BRUTE, true); } else { CALL(ACCEL_BRUTE, false); } }                            \
   } while (0)
 

@@ -14,7 +14,7 @@
 
 namespace rt {
 
-enum { ACCEL_WIDE = 0, ACCEL_BVH2 = 1, ACCEL_BRUTE = 2 };
+enum { ACCEL_WIDE = 0, ACCEL_BVH2 = 1, ACCEL_BRUTE = 2, ACCEL_BVH4 = 3 };
 static const uint32_t RT_MISS = 0xFFFFFFFFu;
 
 // Deepest binary tree a traversal stack is sized for.  An ordered binary traversal holds at most one
@@ -33,7 +33,7 @@ static const uint32_t RT_MISS = 0xFFFFFFFFu;
 #endif
 
 struct BlasDev {
-  const float4* nodes;   // WIDE: 5 x 16 B per node; BVH2: 4 x 16 B per node
+  const float4* nodes;   // WIDE: 5 x 16 B per node; BVH2: 4 x 16 B per node; BVH4: 8 x 16 B per node
   const float4* tris;    // 3 x 16 B per triangle in leaf order: (v0, prim bits) (v1,-) (v2,-)
   const float* verts;    // caller's vertex buffer, stride 6 floats (main.cpp:1678-1683)
   const uint32_t* idx;   // caller's index buffer, 3 per triangle
@@ -328,6 +328,66 @@ RT_HD bool trace_bvh2(const BlasDev& b, const RayObj& r, float tmin, uint32_t in
   return trace_bvh2_direct<Stack, ANY, COUNT>(b, r, tmin, inst, best, st, cnt);
 }
 
+// ---- 4-wide BVH, full-precision boxes (layout: rt_build.cuh::collapse4_node) ------------------------
+// One 128-byte fetch answers two binary levels: half the dependent node fetches per ray of the binary layout,
+// for rays whose time goes into waiting for them (incoherent late bounces, trees that do not fit in L2).
+// The (up to four) children that are hit are visited nearest first: the entry distances, with the child's slot
+// in their two lowest mantissa bits, are sorted by a 5-comparator network of integer min/max (positive floats
+// order like unsigned integers); the order only steers the search - the result is the smallest t with the
+// (instance, primitive) tie rule whatever the order.
+RT_HD int sel4i(int c0, int c1, int c2, int c3, uint32_t i) {
+  const int lo = (i & 1u) ? c1 : c0, hi = (i & 1u) ? c3 : c2;
+  return (i & 2u) ? hi : lo;
+}
+RT_HD void cex_u32(uint32_t& a, uint32_t& b) {
+  const uint32_t lo = a < b ? a : b, hi = a < b ? b : a;
+  a = lo; b = hi;
+}
+
+template <class Stack, bool ANY, bool COUNT>
+RT_HD bool trace_bvh4(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
+                      TravCounters* cnt) {
+  if (b.ntri == 0) return false;
+  if (b.ntri == 1) return test_leaf_tri<ANY, COUNT>(b, 0, r, tmin, inst, best, cnt);
+  st.reset();
+  int node = 0;
+  while (true) {
+    if (node < 0) {
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
+      if (st.empty()) break;
+      node = (int)st.pop1();
+      continue;
+    }
+    const float4* p = b.nodes + 8 * (size_t)node;
+    const float8 A = ldg256(p), B = ldg256(p + 2), Cc = ldg256(p + 4);
+    const float4 D = RT_LDG(p + 6);
+    if (COUNT) cnt->nodes++;
+    const int c0 = (int)f2u(D.x), c1 = (int)f2u(D.y), c2 = (int)f2u(D.z), c3 = (int)f2u(D.w);
+    float tn0, tf0, tn1, tf1, tn2, tf2, tn3, tf3;
+    slab_interval(r, A.a.x, A.b.x, B.a.x, B.b.x, Cc.a.x, Cc.b.x, tmin, best.t, tn0, tf0);
+    slab_interval(r, A.a.y, A.b.y, B.a.y, B.b.y, Cc.a.y, Cc.b.y, tmin, best.t, tn1, tf1);
+    slab_interval(r, A.a.z, A.b.z, B.a.z, B.b.z, Cc.a.z, Cc.b.z, tmin, best.t, tn2, tf2);
+    slab_interval(r, A.a.w, A.b.w, B.a.w, B.b.w, Cc.a.w, Cc.b.w, tmin, best.t, tn3, tf3);
+    // (tn >= tmin > 0: a positive float; a missed or empty child sorts last)
+    uint32_t k0 = (tn0 <= tf0) ? ((f2u(tn0) & ~3u) | 0u) : 0xFFFFFFFFu;
+    uint32_t k1 = (tn1 <= tf1) ? ((f2u(tn1) & ~3u) | 1u) : 0xFFFFFFFFu;
+    uint32_t k2 = (tn2 <= tf2 && c2 != (int)0x80000000) ? ((f2u(tn2) & ~3u) | 2u) : 0xFFFFFFFFu;
+    uint32_t k3 = (tn3 <= tf3 && c3 != (int)0x80000000) ? ((f2u(tn3) & ~3u) | 3u) : 0xFFFFFFFFu;
+    cex_u32(k0, k1); cex_u32(k2, k3); cex_u32(k0, k2); cex_u32(k1, k3); cex_u32(k1, k2);
+    if (k0 == 0xFFFFFFFFu) {   // nothing hit
+      if (st.empty()) break;
+      node = (int)st.pop1();
+      continue;
+    }
+    // far children first, so that the nearest of them is popped first
+    if (k3 != 0xFFFFFFFFu) st.push1((uint32_t)sel4i(c0, c1, c2, c3, k3 & 3u));
+    if (k2 != 0xFFFFFFFFu) st.push1((uint32_t)sel4i(c0, c1, c2, c3, k2 & 3u));
+    if (k1 != 0xFFFFFFFFu) st.push1((uint32_t)sel4i(c0, c1, c2, c3, k1 & 3u));
+    node = sel4i(c0, c1, c2, c3, k0 & 3u);
+  }
+  return false;
+}
+
 // ---- compressed 8-wide BVH --------------------------------------------------------------
 // 80-byte node = 5 x 16 B:
 //   n0 = (p.x, p.y, p.z, ex | ey<<8 | ez<<16 | imask<<24)       quantisation frame + inner mask
@@ -468,6 +528,7 @@ RT_HD bool trace_instance(const SceneDev& s, uint32_t i, f3 o, f3 d, const RayOb
   const BlasDev b = s.blas[in.mesh];  // by value: the node / triangle base pointers stay in registers
   if (s.accel == ACCEL_WIDE) return trace_wide<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
   if (s.accel == ACCEL_BVH2) return trace_bvh2<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
+  if (s.accel == ACCEL_BVH4) return trace_bvh4<Stack, ANY, COUNT>(b, r, tmin, i, best, st, cnt);
   return trace_brute<ANY, COUNT>(b, r, tmin, i, best, cnt);
 }
 

@@ -179,7 +179,7 @@ def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix, t
     n_shadow = st_count["rays_shadow"]
     node_b, tri_b = st_count["node_bytes"], st_count["tri_bytes"]
     trav_bytes = n_node * node_b + n_tri * tri_b + n_closest * (32 + 16 + 4) + n_shadow * (48 + 16)
-    children = 8 if node_b == 80 else 2      # boxes tested per node visit of the active layout
+    children = {80: 8, 128: 4}.get(node_b, 2)      # boxes tested per node visit of the active layout (8-wide / 4-wide / binary)
     trav_flops = n_node * children * 24 + n_tri * 50
     achieved = trav_bytes / (trav_ms * 1e-3) / 1e9
     frame_bytes = (trav_bytes + st_count["n_hit"] * 84 + st_count["n_miss"] * 16 + n_closest * 32 + npix * 4)
@@ -547,7 +547,10 @@ def main():
                      "copy": "frame left on rank 0's GPU, then one device->pinned-host copy"}[e2e_mode],
         "stage_ms": {"trace": round(st_last["trace_ms"], 4), "shadow": round(st_last["shadow_ms"], 4),
                      "shade_raygen_resolve": round(st_last["shade_ms"], 4), "frame_in_library": round(st_last["frame_ms"], 4)},
-        "bvh": {"nodes": st_last["bvh_nodes"], "bytes": st_last["bvh_bytes"]},
+        "bvh": {"nodes": st_last["bvh_nodes"], "bytes": st_last["bvh_bytes"], "node_bytes": st_last["node_bytes"],
+                "layout": {64: "binary, 2 FP32 boxes per 64 B node", 80: "8-wide, quantised, 80 B node",
+                           128: "4-wide, 4 FP32 boxes per 128 B node"}.get(st_last["node_bytes"], "none"),
+                "depth": st_last["max_tree_depth"]},
     }
     if sharded:
         out["gather"] = {

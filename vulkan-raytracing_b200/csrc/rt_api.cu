@@ -9,6 +9,7 @@
 #include <cerrno>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 
@@ -203,9 +204,19 @@ int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
   const uint32_t accel_flag = d->flags & RT_FLAG_ACCEL_MASK;
   if (accel_flag > RT_ACCEL_WIDE4) return fail(RT_ERR_INVALID_ARGUMENT, "unknown accel flag");
   // API flavour -> internal traversal id (template parameter of the kernels)
-  const uint32_t accel = accel_flag == RT_ACCEL_WIDE8 ? (uint32_t)ACCEL_WIDE
-                         : accel_flag == RT_ACCEL_WIDE4 ? (uint32_t)ACCEL_BVH4
-                         : accel_flag == RT_ACCEL_BRUTE ? (uint32_t)ACCEL_BRUTE : (uint32_t)ACCEL_BVH2;
+  uint32_t accel = accel_flag == RT_ACCEL_WIDE8 ? (uint32_t)ACCEL_WIDE
+                   : accel_flag == RT_ACCEL_WIDE4 ? (uint32_t)ACCEL_BVH4
+                   : accel_flag == RT_ACCEL_BRUTE ? (uint32_t)ACCEL_BRUTE : (uint32_t)ACCEL_BVH2;
+  // RT_ACCEL_DEFAULT picks per scene (measured, profiles/r02_wide4.txt): a tree that lives in the 126 MB L2 is
+  // fastest as binary nodes (C3 8.9 vs 10.0 ms); one that does not is faster with 4-wide nodes, which halve the
+  // dependent fetches that then go to HBM (C5a, 9.4 GB: 12.6 vs 14.0 ms).  RT_WIDE4_MIN_MB moves the threshold.
+  bool auto_wide4 = false;
+  if (accel_flag == RT_ACCEL_DEFAULT) {
+    static const double min_mb = getenv("RT_WIDE4_MIN_MB") ? atof(getenv("RT_WIDE4_MIN_MB")) : 256.0;
+    double bytes = 0.0;
+    for (uint32_t i = 0; i < d->n_meshes; i++) bytes += (double)d->meshes[i].n_triangles * (64.0 + 48.0);
+    if (bytes > min_mb * 1e6) { accel = ACCEL_BVH4; auto_wide4 = true; }
+  }
   const bool refine = (d->flags & RT_FLAG_NO_REFINE) == 0;
   for (uint32_t i = 0; i < d->n_meshes; i++) {
     const rt_mesh_desc& m = d->meshes[i];
@@ -248,6 +259,20 @@ int rt_scene_build(const rt_scene_desc* d, void** out_scene) {
   for (uint32_t i = 0; i < d->n_meshes; i++) {
     float one = 0.f;
     int rc = build_blas(s->blas[i], d->meshes[i].n_vertices, d->meshes[i].n_triangles, (int)accel, refine, s->stream, &one, g_err);
+    if (rc == RT_ERR_UNSUPPORTED && auto_wide4) {
+      // the tree is too deep for the 4-wide stack bound (three postponed children per level): the binary layout,
+      // whose bound is three times higher, takes the whole scene instead
+      for (uint32_t k = 0; k <= i; k++) {
+        cudaFree(s->blas[k].d_nodes); cudaFree(s->blas[k].d_tris);
+        s->blas[k].d_nodes = s->blas[k].d_tris = nullptr;
+      }
+      accel = ACCEL_BVH2;
+      s->accel = accel;
+      auto_wide4 = false;
+      ms = 0.f;
+      i = (uint32_t)-1;   // start over
+      continue;
+    }
     if (rc != RT_OK) return rc;
     ms += one;
   }

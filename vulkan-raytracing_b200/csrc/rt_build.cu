@@ -243,6 +243,8 @@ int build_blas(BlasHost& b, uint32_t nvert, uint32_t ntri, int accel, bool refin
   RT_CUDA_TRY(cudaEventCreate(&ev1), err);
   struct EvGuard { cudaEvent_t &a, &b; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); } } ev_guard{ev0, ev1};
   BuildArrays a{};
+  static const uint32_t treelet_min = getenv("RT_TREELET_MIN_LEAVES") ? (uint32_t)atoi(getenv("RT_TREELET_MIN_LEAVES")) : 0u;
+  a.treelet_min_leaves = treelet_min;
   a.verts = b.d_verts;
   a.idx = b.d_idx;
   a.ntri = ntri;

@@ -51,6 +51,9 @@ struct BuildArrays {
   float4* tris;           // 3 x float4 per leaf triangle
   uint32_t* work;         // [max wide nodes] binary node id behind each wide node
   uint32_t* counters;     // [0] wide nodes allocated, [1] leaf triangles allocated
+  // treelet refinement only roots treelets at nodes whose subtree has at least this many triangles (Karras & Aila
+  // 2013, section 4.2: the small subtrees at the bottom are most of the nodes and gain the least); 0 = every node
+  uint32_t treelet_min_leaves;
 };
 
 RT_HD uint32_t float_to_ordered(float f) {
@@ -226,6 +229,13 @@ RT_HD void treelet_optimize_node(const BuildArrays& a, int x, Tables& tab) {
   inner[ni++] = x;
   leaves[0] = RT_LDCG(&a.left[x]);
   leaves[1] = RT_LDCG(&a.right[x]);
+  if (a.treelet_min_leaves) {   // a small subtree keeps its shape: only its SAH cost is needed further up
+    const float4 xlo = RT_LDCG(&a.node_lo[x]);
+    if (f2u(xlo.w) < a.treelet_min_leaves) {
+      a.cost[x] = RT_SAH_CT * half_area(xlo, RT_LDCG(&a.node_hi[x])) + (RT_LDCG(&a.cost[leaves[0]]) + RT_LDCG(&a.cost[leaves[1]]));
+      return;
+    }
+  }
   nl = 2;
   for (int i = 0; i < 2; i++) { llo[i] = RT_LDCG(&a.node_lo[leaves[i]]); lhi[i] = RT_LDCG(&a.node_hi[leaves[i]]); }
   float inner_area = half_area(RT_LDCG(&a.node_lo[x]), RT_LDCG(&a.node_hi[x]));  // sum over the treelet's inner nodes

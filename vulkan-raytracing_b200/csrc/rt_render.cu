@@ -75,6 +75,20 @@ struct HybridStack {
   // 32-bit entries (binary traversal); a packed 2 x STACK_SM word view of the same storage
   // measured 4 % slower than simply using the low half of an 8-byte slot
   __device__ __forceinline__ void push1(uint32_t v) { push(make_uint2(v, 0u)); }
+  // n = 1..3 entries, e1 nearest (popped first).  Usual case: everything lands in the shared-memory part, three
+  // predicated stores and one add instead of three pushes with their shared / local branches
+  __device__ __forceinline__ void push_far_first(int n, uint32_t e1, uint32_t e2, uint32_t e3) {
+    if (sp + 3 <= STACK_SM) {
+      sm[(sp + n - 1) * TRACE_THREADS] = make_uint2(e1, 0u);
+      if (n >= 2) sm[(sp + n - 2) * TRACE_THREADS] = make_uint2(e2, 0u);
+      if (n >= 3) sm[sp * TRACE_THREADS] = make_uint2(e3, 0u);
+      sp += n;
+    } else {
+      if (n >= 3) push1(e3);
+      if (n >= 2) push1(e2);
+      push1(e1);
+    }
+  }
   __device__ __forceinline__ uint32_t pop1() { return pop().x; }
 };
 
@@ -215,7 +229,11 @@ struct TraceSink {
 #ifndef RT_TRACE_MINBLK
 #define RT_TRACE_MINBLK (1024 / RT_TRACE_THREADS)
 #endif
-#define RT_TRACE_BOUNDS __launch_bounds__(TRACE_THREADS, RT_TRACE_MINBLK)
+// the 4-wide layout holds a 128-byte node in registers: RT_BVH4_MINBLK trades resident warps for registers
+#ifndef RT_BVH4_MINBLK
+#define RT_BVH4_MINBLK RT_TRACE_MINBLK
+#endif
+#define RT_TRACE_BOUNDS __launch_bounds__(TRACE_THREADS, (ACCEL == ACCEL_BVH4 ? RT_BVH4_MINBLK : RT_TRACE_MINBLK))
 template <int ACCEL, bool COUNT>
 __global__ void RT_TRACE_BOUNDS
     k_trace(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ rayO,
@@ -447,7 +465,7 @@ struct WaveTraceSink {
 };
 
 template <bool COUNT>
-__global__ void RT_TRACE_BOUNDS
+__global__ void __launch_bounds__(TRACE_THREADS, RT_TRACE_MINBLK)
     k_trace_wave(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ rayO,
                  const float4* __restrict__ rayD, uint4* __restrict__ hits, uint32_t* __restrict__ qMiss,
                  uint32_t* __restrict__ qDiff, uint32_t* __restrict__ qSpec, rt_hit* __restrict__ primary,
@@ -477,7 +495,7 @@ struct WaveShadowSource {
 };
 
 template <bool COUNT>
-__global__ void RT_TRACE_BOUNDS
+__global__ void __launch_bounds__(TRACE_THREADS, RT_TRACE_MINBLK)
     k_shadow_wave(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
                   float4* __restrict__ sample, unsigned long long* __restrict__ stats64, int refill_min, int tri_min) {
   __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];

@@ -344,6 +344,41 @@ RT_HD void cex_u32(uint32_t& a, uint32_t& b) {
   a = lo; b = hi;
 }
 
+// one inner node: `node` becomes the nearest child that is hit (the others are pushed, farthest first) or the next
+// stack entry; false when nothing is left to visit
+template <class Stack, bool COUNT>
+RT_HD bool bvh4_visit(const BlasDev& b, const RayObj& r, float tmin, float tmax, int& node, Stack& st, TravCounters* cnt) {
+  const float4* p = b.nodes + 8 * (size_t)node;
+  const float8 A = ldg256(p), B = ldg256(p + 2), Cc = ldg256(p + 4);
+  const float4 D = RT_LDG(p + 6);
+  if (COUNT) cnt->nodes++;
+  const int c0 = (int)f2u(D.x), c1 = (int)f2u(D.y), c2 = (int)f2u(D.z), c3 = (int)f2u(D.w);
+  float tn0, tf0, tn1, tf1, tn2, tf2, tn3, tf3;
+  slab_interval(r, A.a.x, A.b.x, B.a.x, B.b.x, Cc.a.x, Cc.b.x, tmin, tmax, tn0, tf0);
+  slab_interval(r, A.a.y, A.b.y, B.a.y, B.b.y, Cc.a.y, Cc.b.y, tmin, tmax, tn1, tf1);
+  slab_interval(r, A.a.z, A.b.z, B.a.z, B.b.z, Cc.a.z, Cc.b.z, tmin, tmax, tn2, tf2);
+  slab_interval(r, A.a.w, A.b.w, B.a.w, B.b.w, Cc.a.w, Cc.b.w, tmin, tmax, tn3, tf3);
+  // (tn >= tmin >= 0: a non-negative float orders like its bit pattern; a missed or empty child sorts last;
+  // children 0 and 1 always exist)
+  uint32_t k0 = (tn0 <= tf0) ? ((f2u(tn0) & ~3u) | 0u) : 0xFFFFFFFFu;
+  uint32_t k1 = (tn1 <= tf1) ? ((f2u(tn1) & ~3u) | 1u) : 0xFFFFFFFFu;
+  uint32_t k2 = (tn2 <= tf2 && c2 != (int)0x80000000) ? ((f2u(tn2) & ~3u) | 2u) : 0xFFFFFFFFu;
+  uint32_t k3 = (tn3 <= tf3 && c3 != (int)0x80000000) ? ((f2u(tn3) & ~3u) | 3u) : 0xFFFFFFFFu;
+  cex_u32(k0, k1); cex_u32(k2, k3); cex_u32(k0, k2); cex_u32(k1, k3); cex_u32(k1, k2);
+  if (k0 == 0xFFFFFFFFu) {   // nothing hit
+    if (st.empty()) return false;
+    node = (int)st.pop1();
+    return true;
+  }
+  node = sel4i(c0, c1, c2, c3, k0 & 3u);
+  if (k1 != 0xFFFFFFFFu) {   // more than one child hit: the others go on the stack, farthest first
+    const int nh = 1 + (k2 != 0xFFFFFFFFu ? 1 : 0) + (k3 != 0xFFFFFFFFu ? 1 : 0);
+    st.push_far_first(nh, (uint32_t)sel4i(c0, c1, c2, c3, k1 & 3u), (uint32_t)sel4i(c0, c1, c2, c3, k2 & 3u),
+                      (uint32_t)sel4i(c0, c1, c2, c3, k3 & 3u));
+  }
+  return true;
+}
+
 template <class Stack, bool ANY, bool COUNT>
 RT_HD bool trace_bvh4(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
                       TravCounters* cnt) {
@@ -351,39 +386,41 @@ RT_HD bool trace_bvh4(const BlasDev& b, const RayObj& r, float tmin, uint32_t in
   if (b.ntri == 1) return test_leaf_tri<ANY, COUNT>(b, 0, r, tmin, inst, best, cnt);
   st.reset();
   int node = 0;
+  if (!ANY) {   // closest hit: leaves tested as they are reached (best.t shrinks as early as possible)
+    while (true) {
+      if (node < 0) {
+        if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
+        if (st.empty()) break;
+        node = (int)st.pop1();
+        continue;
+      }
+      if (!bvh4_visit<Stack, COUNT>(b, r, tmin, best.t, node, st, cnt)) break;
+    }
+    return false;
+  }
+  // terminate-on-first-hit rays: the first leaf is parked, the warp tests its leaves together (as trace_bvh2_parked)
+  int parked = RT_NO_LEAF;
+  bool walking = true;
   while (true) {
-    if (node < 0) {
+    while (walking && node >= 0) {
+      walking = bvh4_visit<Stack, COUNT>(b, r, tmin, best.t, node, st, cnt);
+      if (walking && node < 0 && parked == RT_NO_LEAF) {
+        parked = node;
+        if (!st.empty()) node = (int)st.pop1();
+        else walking = false;
+      }
+      if (!RT_ANY_LANE(parked == RT_NO_LEAF && walking)) break;
+    }
+    if (parked != RT_NO_LEAF) {
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~parked, r, tmin, inst, best, cnt)) return true;
+      parked = RT_NO_LEAF;
+    }
+    if (walking && node < 0) {
       if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
-      if (st.empty()) break;
-      node = (int)st.pop1();
-      continue;
+      if (!st.empty()) node = (int)st.pop1();
+      else walking = false;
     }
-    const float4* p = b.nodes + 8 * (size_t)node;
-    const float8 A = ldg256(p), B = ldg256(p + 2), Cc = ldg256(p + 4);
-    const float4 D = RT_LDG(p + 6);
-    if (COUNT) cnt->nodes++;
-    const int c0 = (int)f2u(D.x), c1 = (int)f2u(D.y), c2 = (int)f2u(D.z), c3 = (int)f2u(D.w);
-    float tn0, tf0, tn1, tf1, tn2, tf2, tn3, tf3;
-    slab_interval(r, A.a.x, A.b.x, B.a.x, B.b.x, Cc.a.x, Cc.b.x, tmin, best.t, tn0, tf0);
-    slab_interval(r, A.a.y, A.b.y, B.a.y, B.b.y, Cc.a.y, Cc.b.y, tmin, best.t, tn1, tf1);
-    slab_interval(r, A.a.z, A.b.z, B.a.z, B.b.z, Cc.a.z, Cc.b.z, tmin, best.t, tn2, tf2);
-    slab_interval(r, A.a.w, A.b.w, B.a.w, B.b.w, Cc.a.w, Cc.b.w, tmin, best.t, tn3, tf3);
-    // (tn >= tmin > 0: a positive float; a missed or empty child sorts last)
-    uint32_t k0 = (tn0 <= tf0) ? ((f2u(tn0) & ~3u) | 0u) : 0xFFFFFFFFu;
-    uint32_t k1 = (tn1 <= tf1) ? ((f2u(tn1) & ~3u) | 1u) : 0xFFFFFFFFu;
-    uint32_t k2 = (tn2 <= tf2 && c2 != (int)0x80000000) ? ((f2u(tn2) & ~3u) | 2u) : 0xFFFFFFFFu;
-    uint32_t k3 = (tn3 <= tf3 && c3 != (int)0x80000000) ? ((f2u(tn3) & ~3u) | 3u) : 0xFFFFFFFFu;
-    cex_u32(k0, k1); cex_u32(k2, k3); cex_u32(k0, k2); cex_u32(k1, k3); cex_u32(k1, k2);
-    if (k0 == 0xFFFFFFFFu) {   // nothing hit
-      if (st.empty()) break;
-      node = (int)st.pop1();
-      continue;
-    }
-    // far children first, so that the nearest of them is popped first
-    if (k3 != 0xFFFFFFFFu) st.push1((uint32_t)sel4i(c0, c1, c2, c3, k3 & 3u));
-    if (k2 != 0xFFFFFFFFu) st.push1((uint32_t)sel4i(c0, c1, c2, c3, k2 & 3u));
-    if (k1 != 0xFFFFFFFFu) st.push1((uint32_t)sel4i(c0, c1, c2, c3, k1 & 3u));
-    node = sel4i(c0, c1, c2, c3, k0 & 3u);
+    if (!walking) break;
   }
   return false;
 }
@@ -596,6 +633,12 @@ struct ArrayStack {
   RT_HD void push(uint2 v) { if (sp < N) e[sp++] = v; else RT_FLAG_OVERFLOW(); }
   RT_HD uint2 pop() { return e[--sp]; }
   RT_HD void push1(uint32_t v) { if (sp < N) e[sp++] = make_uint2(v, 0u); else RT_FLAG_OVERFLOW(); }
+  // n = 1..3 entries, e1 nearest: pushed so that e1 is popped first
+  RT_HD void push_far_first(int n, uint32_t e1, uint32_t e2, uint32_t e3) {
+    if (n >= 3) push1(e3);
+    if (n >= 2) push1(e2);
+    push1(e1);
+  }
   RT_HD uint32_t pop1() { return e[--sp].x; }
 };
 

@@ -41,7 +41,7 @@ namespace rt { __device__ uint32_t g_trav_flags; }
 
 namespace rt {
 
-enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_NCULL, C_NSEC, C_STRIDE = 16 };
+enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_NCULL, C_NSEC, C_SHCUR, C_STRIDE = 16 };
 // Block size of the persistent traversal kernels.  One warp per CTA: the warps share nothing but the
 // stack array, and a one-warp CTA hands its slot to the next launch the moment its last batch is done
 // (C3 frame 9.08 ms at 128 threads, 9.01 at 64, 8.93 at 32, 9.24 at 256: r01_sweep_occupancy.txt).
@@ -49,14 +49,21 @@ enum { C_NRAY = 0, C_NMISS, C_NDIFF, C_NSPEC, C_NSHADOW, C_WTRACE, C_WSHADOW, C_
 #define RT_TRACE_THREADS 32
 #endif
 constexpr int TRACE_THREADS = RT_TRACE_THREADS;
-constexpr int STACK_SM = 8;      // stack entries per thread kept in shared memory
+#ifndef RT_STACK_SM
+#define RT_STACK_SM 8
+#endif
+constexpr int STACK_SM = RT_STACK_SM;      // stack entries per thread kept in shared memory
 constexpr int STACK_LOCAL = RT_MAX_TREE_DEPTH - STACK_SM;  // overflow entries in local memory
+// 8-byte words of shared memory per thread: STACK_SM 64-bit entries (8-wide layout), or STACK_SM 32-bit entries plus the
+// 32 bytes of the parked ray (binary / 4-wide layouts, SlimStack)
+constexpr int STACK_U2 = STACK_SM > STACK_SM / 2 + 4 ? STACK_SM : STACK_SM / 2 + 4;
 
 // Traversal stack: the first STACK_SM entries live in shared memory (column per thread,
 // bank-conflict free), the rarely used rest in local memory.
 // The overflow array is a separate local array the struct only points to: with the array inside
 // the struct the compiler kept the whole struct, stack pointer included, in local memory.
 struct HybridStack {
+  typedef uint2 Entry;
   uint2* sm;      // &smem[threadIdx.x], stride blockDim.x
   uint2* loc;     // STACK_LOCAL entries of thread-local memory
   int sp;
@@ -90,14 +97,90 @@ struct HybridStack {
     }
   }
   __device__ __forceinline__ uint32_t pop1() { return pop().x; }
+  __device__ __forceinline__ void init(uint2* smem, Entry* local) { sm = smem + threadIdx.x; loc = local; sp = 0; }
+  __device__ __forceinline__ void park_ray(const RayObj&) {}
+  __device__ __forceinline__ const RayObj& tri_ray(const RayObj& r) const { return r; }
 };
+
+// Stack of the binary and 4-wide layouts (RT_SLIM_STACK, default): 32-bit entries, so the 8 shared-memory entries of a
+// lane take half of the CTA's 2 KB; the other half keeps what only the triangle test reads of the object-space ray
+// (origin, shear constants, axis permutation: 7 words), written once per mesh entry (park_ray) and read back with two
+// LDS.128 at each leaf (tri_ray).  The node loop - where the kernel spends its issue slots and its registers - is left
+// with 1/d and -o/d.  (`volatile` asm: the compiler must not keep the values in registers instead.)
+#ifndef RT_SLIM_STACK
+#define RT_SLIM_STACK 1
+#endif
+struct SlimStack {
+  typedef uint32_t Entry;
+  uint32_t* sm;    // &words[threadIdx.x], stride TRACE_THREADS
+  float4* park;    // &park4[threadIdx.x], two float4 per lane, stride TRACE_THREADS
+  uint32_t* loc;
+  int sp;
+  __device__ __forceinline__ void init(uint2* smem, Entry* local) {
+    sm = (uint32_t*)smem + threadIdx.x;
+    park = (float4*)((uint32_t*)smem + STACK_SM * TRACE_THREADS) + threadIdx.x;
+    loc = local;
+    sp = 0;
+  }
+  __device__ __forceinline__ void reset() { sp = 0; }
+  __device__ __forceinline__ bool empty() const { return sp == 0; }
+  __device__ __forceinline__ void push1(uint32_t v) {
+    if (sp < STACK_SM) sm[sp * TRACE_THREADS] = v;
+    else if (sp < STACK_SM + STACK_LOCAL) loc[sp - STACK_SM] = v;
+    else { RT_FLAG_OVERFLOW(); return; }
+    sp++;
+  }
+  __device__ __forceinline__ uint32_t pop1() {
+    --sp;
+    return sp < STACK_SM ? sm[sp * TRACE_THREADS] : loc[sp - STACK_SM];
+  }
+  __device__ __forceinline__ void push_far_first(int n, uint32_t e1, uint32_t e2, uint32_t e3) {
+    if (sp + 3 <= STACK_SM) {
+      sm[(sp + n - 1) * TRACE_THREADS] = e1;
+      if (n >= 2) sm[(sp + n - 2) * TRACE_THREADS] = e2;
+      if (n >= 3) sm[sp * TRACE_THREADS] = e3;
+      sp += n;
+    } else {
+      if (n >= 3) push1(e3);
+      if (n >= 2) push1(e2);
+      push1(e1);
+    }
+  }
+  // 64-bit entries belong to the 8-wide layout, which never runs on this stack (the calls only have to compile)
+  __device__ __forceinline__ void push(uint2 v) { push1(v.x); }
+  __device__ __forceinline__ uint2 pop() { return make_uint2(pop1(), 0u); }
+  __device__ __forceinline__ void park_ray(const RayObj& r) {
+    park[0] = make_float4(r.o.x, r.o.y, r.o.z, r.Sx);
+    park[TRACE_THREADS] = make_float4(r.Sy, r.Sz, __uint_as_float((uint32_t)(r.kx | (r.ky << 2) | (r.kz << 4))), 0.0f);
+  }
+  __device__ __forceinline__ RayObj tri_ray(const RayObj& r) const {
+    float4 a, b;
+    const unsigned p0 = (unsigned)__cvta_generic_to_shared(park);
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(p0));
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "r"(p0 + 16u * TRACE_THREADS));
+    RayObj t;
+    t.o = mk3(a.x, a.y, a.z);
+    t.Sx = a.w; t.Sy = b.x; t.Sz = b.y;
+    const uint32_t k = __float_as_uint(b.z);
+    t.kx = (int)(k & 3u); t.ky = (int)((k >> 2) & 3u); t.kz = (int)(k >> 4);
+    t.d = r.d; t.idir = r.idir; t.noid = r.noid; t.octinv4 = r.octinv4;   // not used by the triangle test
+    return t;
+  }
+};
+
+// the stack type a layout traverses with
+template <int ACCEL> struct StackFor { typedef HybridStack type; };
+#if RT_SLIM_STACK
+template <> struct StackFor<ACCEL_BVH2> { typedef SlimStack type; };
+template <> struct StackFor<ACCEL_BVH4> { typedef SlimStack type; };
+#endif
 
 template <int ACCEL, bool ANY, bool COUNT>
 __device__ __forceinline__ bool trace_scene_t(const SceneDev& s, f3 o, f3 d, float tmin, float tmax, HitRec& best,
-                                              HybridStack& st, TravCounters* cnt) {
+                                              typename StackFor<ACCEL>::type& st, TravCounters* cnt) {
   SceneDev sc = s;
   sc.accel = ACCEL;  // compile-time constant: the untaken traversal variants fold away
-  return trace_scene<HybridStack, ANY, COUNT>(sc, o, d, tmin, tmax, best, st, cnt);
+  return trace_scene<typename StackFor<ACCEL>::type, ANY, COUNT>(sc, o, d, tmin, tmax, best, st, cnt);
 }
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
@@ -240,11 +323,11 @@ __global__ void RT_TRACE_BOUNDS
             const float4* __restrict__ rayD, uint4* __restrict__ hits, uint32_t* __restrict__ qMiss,
             uint32_t* __restrict__ qDiff, uint32_t* __restrict__ qSpec, rt_hit* __restrict__ primary,
             unsigned long long* __restrict__ stats64, const uint32_t* __restrict__ perm) {
-  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
-  uint2 stack_loc[STACK_LOCAL];
-  HybridStack st;
-  st.sm = &stack_sm[threadIdx.x];
-  st.loc = stack_loc;
+  __shared__ uint2 stack_sm[STACK_U2 * TRACE_THREADS];
+  typedef typename StackFor<ACCEL>::type Stack;
+  typename Stack::Entry stack_loc[STACK_LOCAL];
+  Stack st;
+  st.init(stack_sm, stack_loc);
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NRAY];
   while (true) {
@@ -377,14 +460,21 @@ struct ShadowSink {
 template <int ACCEL, bool COUNT>
 __global__ void RT_TRACE_BOUNDS
     k_shadow(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
-             float4* __restrict__ sample, unsigned long long* __restrict__ stats64) {
-  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
-  uint2 stack_loc[STACK_LOCAL];
-  HybridStack st;
-  st.sm = &stack_sm[threadIdx.x];
-  st.loc = stack_loc;
+             float4* __restrict__ sample, unsigned long long* __restrict__ stats64, const uint32_t* __restrict__ cnt0,
+             uint32_t bounce) {
+  __shared__ uint2 stack_sm[STACK_U2 * TRACE_THREADS];
+  typedef typename StackFor<ACCEL>::type Stack;
+  typename Stack::Entry stack_loc[STACK_LOCAL];
+  Stack st;
+  st.init(stack_sm, stack_loc);
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NSHADOW];
+  if (n == 0u) return;
+  if (cnt0) {   // append-only queue (k_trace_shade): this bounce's rays start behind those of the earlier bounces
+    uint32_t start = 0;
+    for (uint32_t j = 0; j < bounce; j++) start += cnt0[(size_t)j * C_STRIDE + C_NSHADOW];
+    shadowQ += 3 * (size_t)start;
+  }
   while (true) {
     uint32_t base = 0;
     if (lane_id() == 0) base = atomicAdd(&cnt[C_WSHADOW], 32u);
@@ -409,6 +499,113 @@ __global__ void RT_TRACE_BOUNDS
   if (COUNT) {
     atomicAdd(&stats64[2], tc.nodes);
     atomicAdd(&stats64[3], tc.tris);
+  }
+}
+
+// ---- closest hit + the shading of what was hit, one launch per bounce ---------------------------------------
+// traceRayEXT (shader.rgen:86-87) and the rest of the loop body (:90-165) for the rays of one bounce: a lane that has
+// finished its ray runs shader.rmiss / shader.rchit right here instead of handing the hit to k_shade_miss /
+// k_shade_diffuse / k_shade_spec through a hit record and an index queue.  Per bounce and sub-frame that leaves this
+// launch and the shadow launch (4 launches fewer); what it buys is not the launch overhead but the *wait*: the three
+// small kernels could only start when blocks of the other sub-frame's persistent traversal launch retired (all 32 CTA
+// slots and the whole register file of every SM are taken), which left 0.1-0.5 ms between consecutive closest-hit
+// launches of a sub-frame in bounces >= 3, where the frame is a chain of short launches (profiles/r02_fused_shade.txt).
+// Shadow rays are appended to a queue that only grows during the frame (every path emits at most one): the shadow
+// launch of bounce j reads its part while bounce j + 1 already appends behind it, so nothing waits for a shadow launch.
+template <int ACCEL, bool COUNT>
+__global__ void RT_TRACE_BOUNDS
+    k_trace_shade(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt0, uint32_t bounce, const float4* __restrict__ rayO,
+                  const float4* __restrict__ rayD, float4* __restrict__ nextO, float4* __restrict__ nextD,
+                  float4* __restrict__ shadowQ, float4* __restrict__ sample, rt_hit* __restrict__ primary,
+                  unsigned long long* __restrict__ stats64) {
+  __shared__ uint2 stack_sm[STACK_U2 * TRACE_THREADS];
+  typedef typename StackFor<ACCEL>::type Stack;
+  typename Stack::Entry stack_loc[STACK_LOCAL];
+  Stack st;
+  st.init(stack_sm, stack_loc);
+  TravCounters tc{0ull, 0ull};
+  uint32_t* cnt = cnt0 + (size_t)bounce * C_STRIDE;
+  uint32_t* cntNext = cnt + C_STRIDE;
+  const uint32_t n = cnt[C_NRAY];
+  const bool last = bounce >= U.max_bounce;   // the loop of shader.rgen:84 runs j = 0..maxBounceCount
+  uint32_t n_miss = 0, n_diff = 0, n_spec = 0, n_shadow = 0;
+  while (true) {
+    uint32_t base = 0;
+    if (lane_id() == 0) base = atomicAdd(&cnt[C_WTRACE], 32u);
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (base >= n) break;
+    const uint32_t idx = base + lane_id();
+    bool emit = false, cont = false;
+    f3 P = mk3(0, 0, 0), N = mk3(0, 0, 0), o = mk3(0, 0, 0), d = mk3(0, 0, 0), dn = mk3(0, 0, 0);
+    uint32_t slot = 0, inst = 0;
+    if (idx < n) {
+      const float4 ro = rayO[idx], rd = rayD[idx];
+      slot = __float_as_uint(ro.w);
+      o = mk3(ro.x, ro.y, ro.z);
+      d = mk3(rd.x, rd.y, rd.z);
+      HitRec h;
+      const bool hit = trace_scene_t<ACCEL, false, COUNT>(scene, o, d, 0.001f, 10000.0f, h, st, &tc);   // shader.rgen:86-87
+      if (primary) {
+        uint32_t x, y;
+        slot_to_pixel(U, slot / U.spp, x, y);
+        rt_hit out;
+        out.instance = h.inst; out.primitive = h.prim; out.t = hit ? h.t : 0.0f; out.u = h.u; out.v = h.v;
+        primary[((size_t)y * U.width + x) * U.spp + (slot % U.spp)] = out;
+      }
+      if (!hit) {   // shader.rmiss + shader.rgen:90-94
+        const f3 c = sky_sample(scene, mk3(d.x, d.y, -d.z));
+        sample[slot] = make_float4(c.x, c.y, c.z, 1.0f);
+        n_miss++;
+      } else {
+        inst = h.inst;
+        rchit(scene, h.inst, h.prim, h.u, h.v, P, N);
+        const uint32_t type = scene.inst[h.inst].type;
+        if (type == 0u) {   // diffuse, shader.rgen:97-110: a back face keeps the ambient colour, a front face asks the light
+          n_diff++;
+          emit = !(dot3(d, N) >= 0.0f);
+          if (emit && scene.mat) {   // rt_scene_set_materials: the surface's own ambient term, lit or not
+            const f3 amb = material_ambient(scene.mat[inst]);
+            sample[slot] = make_float4(amb.x, amb.y, amb.z, 1.0f);
+          }
+        } else {            // mirror / refraction, shader.rgen:132-165
+          n_spec++;
+          if (!last) {
+            dn = d;
+            scatter(type, P, N, o, dn, scene.mat ? scene.mat[inst].ni : 1.52f);
+            cont = true;
+          }
+        }
+      }
+    }
+    uint32_t dst = warp_append(emit, &cnt0[C_SHCUR]);
+    if (emit) {
+      n_shadow++;
+      shadowQ[3 * (size_t)dst + 0] = make_float4(P.x, P.y, P.z, __uint_as_float(slot));
+      shadowQ[3 * (size_t)dst + 1] = make_float4(N.x, N.y, N.z, __uint_as_float(inst));
+      shadowQ[3 * (size_t)dst + 2] = make_float4(d.x, d.y, d.z, 0.0f);
+    }
+    dst = warp_append(cont, &cntNext[C_NRAY]);
+    if (cont) {
+      nextO[dst] = make_float4(o.x, o.y, o.z, __uint_as_float(slot));
+      nextD[dst] = make_float4(dn.x, dn.y, dn.z, 0.0f);
+    }
+  }
+#pragma unroll
+  for (int k = 16; k > 0; k >>= 1) {
+    n_miss += __shfl_xor_sync(0xFFFFFFFFu, n_miss, k);
+    n_diff += __shfl_xor_sync(0xFFFFFFFFu, n_diff, k);
+    n_spec += __shfl_xor_sync(0xFFFFFFFFu, n_spec, k);
+    n_shadow += __shfl_xor_sync(0xFFFFFFFFu, n_shadow, k);
+  }
+  if (lane_id() == 0) {
+    if (n_miss) atomicAdd(&cnt[C_NMISS], n_miss);
+    if (n_diff) atomicAdd(&cnt[C_NDIFF], n_diff);
+    if (n_spec) atomicAdd(&cnt[C_NSPEC], n_spec);
+    if (n_shadow) atomicAdd(&cnt[C_NSHADOW], n_shadow);
+  }
+  if (COUNT) {
+    atomicAdd(&stats64[0], tc.nodes);
+    atomicAdd(&stats64[1], tc.tris);
   }
 }
 
@@ -470,7 +667,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, RT_TRACE_MINBLK)
                  const float4* __restrict__ rayD, uint4* __restrict__ hits, uint32_t* __restrict__ qMiss,
                  uint32_t* __restrict__ qDiff, uint32_t* __restrict__ qSpec, rt_hit* __restrict__ primary,
                  unsigned long long* __restrict__ stats64, int refill_min, int tri_min, const uint32_t* __restrict__ perm) {
-  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  __shared__ uint2 stack_sm[STACK_U2 * TRACE_THREADS];
   uint2 stack_loc[STACK_LOCAL];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
@@ -498,7 +695,7 @@ template <bool COUNT>
 __global__ void __launch_bounds__(TRACE_THREADS, RT_TRACE_MINBLK)
     k_shadow_wave(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
                   float4* __restrict__ sample, unsigned long long* __restrict__ stats64, int refill_min, int tri_min) {
-  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
+  __shared__ uint2 stack_sm[STACK_U2 * TRACE_THREADS];
   uint2 stack_loc[STACK_LOCAL];
   HybridStack st;
   st.sm = &stack_sm[threadIdx.x];
@@ -651,11 +848,11 @@ template <int ACCEL, bool ANY, bool COUNT>
 __global__ void __launch_bounds__(TRACE_THREADS)
     k_trace_batch(SceneDev scene, uint64_t n, const float* __restrict__ o, const float* __restrict__ d, float tmin,
                   float tmax, rt_hit* __restrict__ out, unsigned long long* __restrict__ stats64) {
-  __shared__ uint2 stack_sm[STACK_SM * TRACE_THREADS];
-  uint2 stack_loc[STACK_LOCAL];
-  HybridStack st;
-  st.sm = &stack_sm[threadIdx.x];
-  st.loc = stack_loc;
+  __shared__ uint2 stack_sm[STACK_U2 * TRACE_THREADS];
+  typedef typename StackFor<ACCEL>::type Stack;
+  typename Stack::Entry stack_loc[STACK_LOCAL];
+  Stack st;
+  st.init(stack_sm, stack_loc);
   TravCounters tc{0ull, 0ull};
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
     HitRec h;
@@ -825,6 +1022,9 @@ static int pipeline_reserve(FramePipeline* p, size_t slots, size_t bounces, std:
 
 template <class K>
 static int persistent_blocks(K kernel, int threads) {
+  // RT_CARVEOUT = percent of the SM's 228 KB the traversal kernels ask for as shared memory (a hint; the rest is L1)
+  static const int carve = getenv("RT_CARVEOUT") ? atoi(getenv("RT_CARVEOUT")) : -1;
+  if (carve >= 0) cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
   int per_sm = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
   return per_sm * sm_count();
@@ -903,6 +1103,10 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   static const int path_leaf = getenv("RT_PATH_LEAF") ? atoi(getenv("RT_PATH_LEAF")) : 8;
   static const int path_left = getenv("RT_PATH_LEFT") ? atoi(getenv("RT_PATH_LEFT")) : 3;
   static const int path_chunk = getenv("RT_PATH_CHUNK") ? atoi(getenv("RT_PATH_CHUNK")) : 64;
+  // Shading inside the closest-hit launch (k_trace_shade), the default; RT_FUSE_SHADE=0 puts the three shading kernels
+  // back between the traversal launches.  Ray reordering and the warp-synchronous 8-wide variant keep the separate kernels.
+  static const bool fuse_shade_env = getenv("RT_FUSE_SHADE") ? atoi(getenv("RT_FUSE_SHADE")) != 0 : true;
+  const bool fuse_shade = fuse_shade_env && !may_sort && !(accel == ACCEL_WIDE && wave_on && rq.scene.tlas == nullptr);
   const bool fused = fused_env && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && !may_sort && rq.scene.n_inst <= 32u;
   const int nsub = (sub_env >= 2 && nslots >= sub_min_slots && !may_sort && !wave)
                        ? (int)std::min<uint32_t>((uint32_t)std::min(sub_env, RT_MAX_SUB), U.n_local_tiles) : 1;
@@ -978,6 +1182,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     uint32_t* cn = c.cnt + (size_t)(j + 1) * C_STRIDE;
     rt_hit* prim = (j == 0 && rq.want_primary) ? rq.d_primary : nullptr;
     const uint32_t* perm = c.perm;
+    const uint32_t* sh_cnt0 = nullptr;   // the shadow queue is refilled from its start by every bounce
 #define CALL_TRACE(A, C)                                                                                          \
   {                                                                                                               \
     static int blocks = 0;                                                                                        \
@@ -1006,7 +1211,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   {                                                                                                       \
     static int blocks = 0;                                                                                \
     if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
-    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64); \
+    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j); \
   }
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 2], sst), err);
     if (wave) {
@@ -1038,6 +1243,54 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
       // Deep bounce limits (MAX_BOUNCE_COUNT 63): stop as soon as no ray survives.  The count
       // travels to pinned memory behind the bounce; bounces 1-8 only look at counts that have
       // already landed (no stall), deeper ones wait for theirs.
+      RT_CUDA_TRY(cudaMemcpyAsync(&sb.h_alive[j + 1], cn + C_NRAY, sizeof(uint32_t), cudaMemcpyDeviceToHost, cs), err);
+      RT_CUDA_TRY(cudaEventRecord(sb.aev[j + 1], cs), err);
+      if (j + 1 > 8) { RT_CUDA_TRY(cudaEventSynchronize(sb.aev[j + 1]), err); }
+      for (uint32_t k = 1; k <= j + 1 && !c.dead; k++)
+        c.dead = cudaEventQuery(sb.aev[k]) == cudaSuccess && sb.h_alive[k] == 0u;
+    }
+    return RT_OK;
+  };
+  // one bounce of one sub-frame with the shading done by the closest-hit launch itself (k_trace_shade): two launches,
+  // and nothing on the sub-frame's main stream ever waits for a shadow launch
+  auto enqueue_bounce_fused = [&](SubCtx& c, uint32_t j) -> int {
+    FramePipeline::Sub& sb = *c.sb;
+    cudaStream_t cs = c.st, sst = c.sst;
+    const int cur = c.cur;
+    uint32_t* cj = c.cnt + (size_t)j * C_STRIDE;
+    uint32_t* cn = c.cnt + (size_t)(j + 1) * C_STRIDE;
+    rt_hit* prim = (j == 0 && rq.want_primary) ? rq.d_primary : nullptr;
+    const uint32_t* sh_cnt0 = c.cnt;
+#define CALL_TRACE_SHADE(A, C)                                                                                        \
+  {                                                                                                                   \
+    static int blocks = 0;                                                                                            \
+    if (!blocks) blocks = persistent_blocks(k_trace_shade<A, C>, TRACE_THREADS);                                      \
+    k_trace_shade<A, C><<<blocks, TRACE_THREADS, 0, cs>>>(rq.scene, U, c.cnt, j, c.rayO[cur], c.rayD[cur], c.rayO[cur ^ 1], \
+                                                          c.rayD[cur ^ 1], c.shadowQ, p->sample, prim, p->stats64);    \
+  }
+#define CALL_SHADOW_F(A, C)                                                                               \
+  {                                                                                                       \
+    static int blocks = 0;                                                                                \
+    if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
+    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j); \
+  }
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 0], cs), err);
+    RT_DISPATCH_ACCEL(accel, counting, CALL_TRACE_SHADE);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 1], cs), err);
+    if (shadow_async) {
+      RT_CUDA_TRY(cudaEventRecord(sb.sev[2 * j], cs), err);
+      RT_CUDA_TRY(cudaStreamWaitEvent(sst, sb.sev[2 * j], 0), err);
+    }
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 2], sst), err);
+    RT_DISPATCH_ACCEL(accel, counting, CALL_SHADOW_F);
+    RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 3], sst), err);
+    if (shadow_async) RT_CUDA_TRY(cudaEventRecord(sb.sev[2 * j + 1], sst), err);
+#undef CALL_TRACE_SHADE
+#undef CALL_SHADOW_F
+    launches += 2;
+    c.last_bounce = j;
+    if (j < U.max_bounce) {
+      c.cur ^= 1;
       RT_CUDA_TRY(cudaMemcpyAsync(&sb.h_alive[j + 1], cn + C_NRAY, sizeof(uint32_t), cudaMemcpyDeviceToHost, cs), err);
       RT_CUDA_TRY(cudaEventRecord(sb.aev[j + 1], cs), err);
       if (j + 1 > 8) { RT_CUDA_TRY(cudaEventSynchronize(sb.aev[j + 1]), err); }
@@ -1091,7 +1344,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     bool any = false;
     for (int k = 0; k < nsub; k++) {
       if (ctx[k].dead) continue;
-      rc = enqueue_bounce(ctx[k], j);
+      rc = fuse_shade ? enqueue_bounce_fused(ctx[k], j) : enqueue_bounce(ctx[k], j);
       if (rc != RT_OK) return rc;
       any = any || !ctx[k].dead;
     }

@@ -86,6 +86,9 @@ struct RayObj {
   int kx, ky, kz;
   float Sx, Sy, Sz;
   f3 idir;          // 1/d with |d| clamped away from 0 (box tests only)
+  f3 noid;          // -o * idir: plane distance = fma(plane, idir, noid) (binary / 4-wide node test)
+  f3 ipos, ineg;    // idir split by sign: (idir, 0) where idir >= 0, else (0, idir) - the near / far plane is
+                    // picked by multiplying the other one with 0 (slab_interval_sel)
   uint32_t octinv4; // (dx>=0?4:0 | dy>=0?2:0 | dz>=0?1:0) replicated in 4 bytes
 };
 
@@ -123,6 +126,9 @@ RT_HD RayObj ray_setup(f3 o, f3 d) {
   r.Sy = sel3(d, ky) / dz;
   r.Sz = 1.0f / dz;
   r.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
+  r.noid = mk3(-o.x * r.idir.x, -o.y * r.idir.y, -o.z * r.idir.z);
+  r.ipos = mk3(r.idir.x >= 0.0f ? r.idir.x : 0.0f, r.idir.y >= 0.0f ? r.idir.y : 0.0f, r.idir.z >= 0.0f ? r.idir.z : 0.0f);
+  r.ineg = mk3(r.idir.x >= 0.0f ? 0.0f : r.idir.x, r.idir.y >= 0.0f ? 0.0f : r.idir.y, r.idir.z >= 0.0f ? 0.0f : r.idir.z);
   // signs taken from idir, the value the plane distances are multiplied with: for d = -0 the
   // clamped reciprocal is negative while "d >= 0" would say positive
   r.octinv4 = ((r.idir.x >= 0.0f ? 4u : 0u) | (r.idir.y >= 0.0f ? 2u : 0u) | (r.idir.z >= 0.0f ? 1u : 0u)) * 0x01010101u;
@@ -218,6 +224,50 @@ RT_HD void slab_interval(const RayObj& r, float lox, float loy, float loz, float
   tf = fminf(fmaf(1e-5f, fabsf(f), f), tmax);
 }
 
+// The same interval with one fma per plane (12 instead of 24 FP32 instructions per binary node; the node test is
+// what the closest-hit kernel issues most).  plane * idir is exact inside the fma, so the only new error is the
+// rounding of noid = -o * idir: |o| * 2^-24 in space units, far below the leaf padding of 4e-6 * max |coordinate|
+// for origins within 60 mesh extents, and below the relative margin on t for origins farther away.  One
+// multiplication widens the interval: hit <=> max(n, tmin) <= min(f, tmax) * (1 + 2e-5), which contains the
+// [n (1 - 1e-5), f (1 + 1e-5)] test of slab_interval for every positive far distance (a box whose far distance
+// is negative lies behind the origin and fails both).  Box culling only has to be conservative.
+RT_HD void slab_interval_fma(const RayObj& r, float lox, float loy, float loz, float hix, float hiy, float hiz, float tmin,
+                             float tmax, float& tn, float& tf) {
+  const float t1x = fmaf(lox, r.idir.x, r.noid.x), t2x = fmaf(hix, r.idir.x, r.noid.x);
+  const float t1y = fmaf(loy, r.idir.y, r.noid.y), t2y = fmaf(hiy, r.idir.y, r.noid.y);
+  const float t1z = fmaf(loz, r.idir.z, r.noid.z), t2z = fmaf(hiz, r.idir.z, r.noid.z);
+  const float n = fmaxf(fmaxf(fminf(t1x, t2x), fminf(t1y, t2y)), fminf(t1z, t2z));
+  const float f = fminf(fminf(fmaxf(t1x, t2x), fmaxf(t1y, t2y)), fmaxf(t1z, t2z));
+  tn = fmaxf(n, tmin);
+  tf = fminf(f, tmax) * 1.00002f;
+}
+
+// The same distances with the near and far plane of each axis picked by the ray's direction signs *in the FMA pipe*:
+// near = fma(lo, ipos, fma(hi, ineg, noid)) is fma(lo, idir, noid) for idir >= 0 and fma(hi, idir, noid) otherwise
+// (the product with 0 adds exactly nothing), far likewise with lo and hi exchanged.  12 more FFMA replace the 12
+// FMNMX of the per-axis min / max: on sm_100a FMNMX, FSETP and SEL share the half-rate ALU pipe, which ncu shows at
+// 60-63 % in the closest-hit kernel against 22 % for the FMA pipe (profiles/r02_slab_fma.txt).
+RT_HD void slab_interval_sel(const RayObj& r, float lox, float loy, float loz, float hix, float hiy, float hiz, float tmin,
+                             float tmax, float& tn, float& tf) {
+  const float nx = fmaf(lox, r.ipos.x, fmaf(hix, r.ineg.x, r.noid.x)), fx = fmaf(hix, r.ipos.x, fmaf(lox, r.ineg.x, r.noid.x));
+  const float ny = fmaf(loy, r.ipos.y, fmaf(hiy, r.ineg.y, r.noid.y)), fy = fmaf(hiy, r.ipos.y, fmaf(loy, r.ineg.y, r.noid.y));
+  const float nz = fmaf(loz, r.ipos.z, fmaf(hiz, r.ineg.z, r.noid.z)), fz = fmaf(hiz, r.ipos.z, fmaf(loz, r.ineg.z, r.noid.z));
+  tn = fmaxf(fmaxf(fmaxf(nx, ny), nz), tmin);
+  tf = fminf(fminf(fminf(fx, fy), fz), tmax) * 1.00002f;
+}
+
+// RT_SLAB_FMA=0 builds the subtract-then-multiply test back in, 1 the one-fma form with per-axis min / max (the A/B of profiles/r02_slab_fma.txt)
+#ifndef RT_SLAB_FMA
+#define RT_SLAB_FMA 1
+#endif
+#if RT_SLAB_FMA == 2
+#define RT_SLAB slab_interval_sel
+#elif RT_SLAB_FMA == 1
+#define RT_SLAB slab_interval_fma
+#else
+#define RT_SLAB slab_interval
+#endif
+
 // Ordered traversal with a postponed leaf (Aila & Laine 2009, "speculative traversal").  Leaves
 // are single triangles and turn up once per ~15 node visits, at different moments in different
 // lanes: tested on the spot, the triangle code ran with 5 of 32 lanes and took 38 % of the issue
@@ -231,6 +281,7 @@ template <class Stack, bool ANY, bool COUNT>
 RT_HD bool trace_bvh2_parked(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
                              TravCounters* cnt) {
   st.reset();
+  st.park_ray(r);
   int node = 0, parked = RT_NO_LEAF;
   bool walking = true;  // `node` is valid (an inner node to visit or a leaf to test)
   while (true) {
@@ -239,8 +290,8 @@ RT_HD bool trace_bvh2_parked(const BlasDev& b, const RayObj& r, float tmin, uint
       const float4 n0 = lo8.a, n1 = lo8.b, n2 = hi8.a, n3 = hi8.b;
       if (COUNT) cnt->nodes++;
       float tn0, tf0, tn1, tf1;
-      slab_interval(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
-      slab_interval(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
+      RT_SLAB(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
+      RT_SLAB(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
       const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
       int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
       if (h0 && h1) {
@@ -264,11 +315,11 @@ RT_HD bool trace_bvh2_parked(const BlasDev& b, const RayObj& r, float tmin, uint
       if (!RT_ANY_LANE(parked == RT_NO_LEAF && walking)) break;  // every lane has something to test
     }
     if (parked != RT_NO_LEAF) {
-      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~parked, r, tmin, inst, best, cnt)) return true;
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~parked, st.tri_ray(r), tmin, inst, best, cnt)) return true;
       parked = RT_NO_LEAF;
     }
     if (walking && node < 0) {
-      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, st.tri_ray(r), tmin, inst, best, cnt)) return true;
       if (!st.empty()) node = (int)st.pop1();
       else walking = false;
     }
@@ -282,10 +333,11 @@ template <class Stack, bool ANY, bool COUNT>
 RT_HD bool trace_bvh2_direct(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best, Stack& st,
                              TravCounters* cnt) {
   st.reset();
+  st.park_ray(r);
   int node = 0;
   while (true) {
     if (node < 0) {
-      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, st.tri_ray(r), tmin, inst, best, cnt)) return true;
       if (st.empty()) break;
       node = (int)st.pop1();
       continue;
@@ -293,11 +345,14 @@ RT_HD bool trace_bvh2_direct(const BlasDev& b, const RayObj& r, float tmin, uint
     const float8 lo8 = ldg256(&b.nodes[4 * (size_t)node]), hi8 = ldg256(&b.nodes[4 * (size_t)node + 2]);
     const float4 n0 = lo8.a, n1 = lo8.b, n2 = hi8.a, n3 = hi8.b;
     if (COUNT) cnt->nodes++;
+#ifdef RT_EXTRA_LOAD   // experiment: one more L1 request per node visit, same cache line, result (never true) consumed
+    { const float4 ex = RT_LDG(&b.nodes[4 * (size_t)node + 1]); if (ex.x == 1.2345e33f) best.t = 0.0f; }
+#endif
     float tn0, tf0, tn1, tf1;
     // (a one-fma-per-plane form with the margins folded into per-ray constants was measured: 12 more
     // live registers cost more than the 16 instructions per node it saves, profiles/r01_sweep_boxtest.txt)
-    slab_interval(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
-    slab_interval(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
+    RT_SLAB(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
+    RT_SLAB(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
     const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
     int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
     if (h0 && h1) {
@@ -354,10 +409,10 @@ RT_HD bool bvh4_visit(const BlasDev& b, const RayObj& r, float tmin, float tmax,
   if (COUNT) cnt->nodes++;
   const int c0 = (int)f2u(D.x), c1 = (int)f2u(D.y), c2 = (int)f2u(D.z), c3 = (int)f2u(D.w);
   float tn0, tf0, tn1, tf1, tn2, tf2, tn3, tf3;
-  slab_interval(r, A.a.x, A.b.x, B.a.x, B.b.x, Cc.a.x, Cc.b.x, tmin, tmax, tn0, tf0);
-  slab_interval(r, A.a.y, A.b.y, B.a.y, B.b.y, Cc.a.y, Cc.b.y, tmin, tmax, tn1, tf1);
-  slab_interval(r, A.a.z, A.b.z, B.a.z, B.b.z, Cc.a.z, Cc.b.z, tmin, tmax, tn2, tf2);
-  slab_interval(r, A.a.w, A.b.w, B.a.w, B.b.w, Cc.a.w, Cc.b.w, tmin, tmax, tn3, tf3);
+  RT_SLAB(r, A.a.x, A.b.x, B.a.x, B.b.x, Cc.a.x, Cc.b.x, tmin, tmax, tn0, tf0);
+  RT_SLAB(r, A.a.y, A.b.y, B.a.y, B.b.y, Cc.a.y, Cc.b.y, tmin, tmax, tn1, tf1);
+  RT_SLAB(r, A.a.z, A.b.z, B.a.z, B.b.z, Cc.a.z, Cc.b.z, tmin, tmax, tn2, tf2);
+  RT_SLAB(r, A.a.w, A.b.w, B.a.w, B.b.w, Cc.a.w, Cc.b.w, tmin, tmax, tn3, tf3);
   // (tn >= tmin >= 0: a non-negative float orders like its bit pattern; a missed or empty child sorts last;
   // children 0 and 1 always exist)
   uint32_t k0 = (tn0 <= tf0) ? ((f2u(tn0) & ~3u) | 0u) : 0xFFFFFFFFu;
@@ -385,11 +440,12 @@ RT_HD bool trace_bvh4(const BlasDev& b, const RayObj& r, float tmin, uint32_t in
   if (b.ntri == 0) return false;
   if (b.ntri == 1) return test_leaf_tri<ANY, COUNT>(b, 0, r, tmin, inst, best, cnt);
   st.reset();
+  st.park_ray(r);
   int node = 0;
   if (!ANY) {   // closest hit: leaves tested as they are reached (best.t shrinks as early as possible)
     while (true) {
       if (node < 0) {
-        if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
+        if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, st.tri_ray(r), tmin, inst, best, cnt)) return true;
         if (st.empty()) break;
         node = (int)st.pop1();
         continue;
@@ -412,11 +468,11 @@ RT_HD bool trace_bvh4(const BlasDev& b, const RayObj& r, float tmin, uint32_t in
       if (!RT_ANY_LANE(parked == RT_NO_LEAF && walking)) break;
     }
     if (parked != RT_NO_LEAF) {
-      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~parked, r, tmin, inst, best, cnt)) return true;
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~parked, st.tri_ray(r), tmin, inst, best, cnt)) return true;
       parked = RT_NO_LEAF;
     }
     if (walking && node < 0) {
-      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, r, tmin, inst, best, cnt)) return true;
+      if (test_leaf_tri<ANY, COUNT>(b, (uint32_t)~node, st.tri_ray(r), tmin, inst, best, cnt)) return true;
       if (!st.empty()) node = (int)st.pop1();
       else walking = false;
     }
@@ -640,6 +696,9 @@ struct ArrayStack {
     push1(e1);
   }
   RT_HD uint32_t pop1() { return e[--sp].x; }
+  // (the GPU's SlimStack keeps the triangle-test half of the ray in shared memory; here it stays where it is)
+  RT_HD void park_ray(const RayObj&) {}
+  RT_HD const RayObj& tri_ray(const RayObj& r) const { return r; }
 };
 
 }  // namespace rt

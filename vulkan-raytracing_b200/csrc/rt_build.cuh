@@ -23,6 +23,19 @@ template <class T> inline T emu_atomic_add(T* p, T v) { T o = *p; *p = o + v; re
 
 namespace rt {
 
+// An array seen through a stride.  The GPU build interleaves what a node visit reads together - box min | box max |
+// subtree cost in one 32-byte sector, left | right child in one 8-byte pair - because every access of the bottom-up
+// passes is a scattered one and costs a 32-byte DRAM sector whatever it uses of it (the 84 M-triangle treelet rounds
+// moved 14 GB per round at 4-16 useful bytes per sector).  The emulation keeps plain arrays (stride 1).
+template <class T>
+struct StridedArray {
+  T* base;
+  uint32_t stride;
+  RT_HD T& operator[](size_t i) const { return base[i * stride]; }
+  StridedArray& operator=(T* p) { base = p; stride = 1; return *this; }
+  void set(T* p, uint32_t s) { base = p; stride = s; }
+};
+
 // Everything the build of one mesh reads and writes (device pointers).
 struct BuildArrays {
   // inputs
@@ -39,13 +52,13 @@ struct BuildArrays {
   uint32_t* vals;         // triangle ids in Morton order
   // binary radix tree: internal nodes [0, ntri-1), leaf j has id (ntri-1)+j
   int32_t* parent;        // [2*ntri-1]
-  int32_t* left;          // [ntri-1]
-  int32_t* right;         // [ntri-1]
+  StridedArray<int32_t> left;   // [ntri-1]
+  StridedArray<int32_t> right;  // [ntri-1]
   uint32_t* first;        // [ntri-1] first leaf covered
-  float4* node_lo;        // [2*ntri-1] xyz = box min, w = leaf count (as uint bits)
-  float4* node_hi;        // [2*ntri-1]
+  StridedArray<float4> node_lo; // [2*ntri-1] xyz = box min, w = leaf count (as uint bits)
+  StridedArray<float4> node_hi; // [2*ntri-1] (on the GPU w is where `cost` lives: always written after the box)
   uint32_t* flags;        // [ntri-1] arrival counters of the bottom-up passes
-  float* cost;            // [2*ntri-1] SAH cost of the subtree (treelet refinement)
+  StridedArray<float> cost;     // [2*ntri-1] SAH cost of the subtree (treelet refinement)
   // wide output
   uint4* wide;            // 5 x uint4 per node
   float4* tris;           // 3 x float4 per leaf triangle

@@ -173,12 +173,15 @@ def load_peaks():
 
 
 def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix, traffic_applies=True):
-    """Algorithmic work of the traversal kernels (k_trace + k_shadow) of one frame, DESIGN.md §5."""
+    """Algorithmic work of the traversal kernels (k_trace_shade + k_shadow) of one frame, DESIGN.md §5."""
     n_node, n_tri = st_count["nodes_visited"], st_count["tris_tested"]
     n_closest = st_count["rays_primary"] + st_count["rays_secondary"] - st_count.get("rays_top_level", 0)  # rays in the queue
     n_shadow = st_count["rays_shadow"]
     node_b, tri_b = st_count["node_bytes"], st_count["tri_bytes"]
-    trav_bytes = n_node * node_b + n_tri * tri_b + n_closest * (32 + 16 + 4) + n_shadow * (48 + 16)
+    # ray state of the fused closest-hit + shading launch: 32 B read per traced ray, 32 B written per continuation ray, 48 B
+    # per shadow ray appended; the shadow launch reads those 48 B and writes the 16 B radiance slot of an unoccluded one
+    trav_bytes = (n_node * node_b + n_tri * tri_b + n_closest * 32 + st_count["rays_secondary"] * 32
+                  + n_shadow * (48 + 48 + 16))
     children = {80: 8, 128: 4}.get(node_b, 2)      # boxes tested per node visit of the active layout (8-wide / 4-wide / binary)
     trav_flops = n_node * children * 24 + n_tri * 50
     achieved = trav_bytes / (trav_ms * 1e-3) / 1e9
@@ -204,7 +207,7 @@ def roofline(st_count, trav_ms, frame_ms, hbm_gbs, hbm_src, fp32_tflops, npix, t
         except Exception as e:
             ncu_note = f"profiles/traffic.json unreadable: {e}"
     return {
-        "bound": "hbm", "kernel": "k_trace+k_shadow (all traversal launches of one frame)",
+        "bound": "hbm", "kernel": "k_trace_shade+k_shadow (all traversal launches of one frame)",
         "achieved": round(achieved, 1), "peak": hbm_gbs, "peak_source": hbm_src, "unit": "GB/s",
         "frac": round(achieved / hbm_gbs, 4), "traffic": traffic,
         "frac_algorithmic_cache_blind": round(achieved / hbm_gbs, 4),

@@ -42,6 +42,7 @@ WORKLOADS = {
     "c2": ("c2_scene", 1920, 1080, 4, 4),
     "c5a": ("c5a_scene", 3840, 2160, 8, 4),
     "c5b": ("c5b_scene", 3840, 2160, 8, 4),
+    "c1": ("c1_bench_scene", 800, 600, 63, 4),
 }
 WORKLOAD_TEXT = {
     "c3": "C3 armadillo_standin(327680 tri, refractive, T(0,0,5)) + teapot(diffuse, shadow rays) 3840x2160 spp4 depth8",
@@ -49,6 +50,7 @@ WORKLOAD_TEXT = {
     "c2": "C2 teapot(mirror) + teapot(refractive, T(0,0,5)) 1920x1080 spp4 depth4",
     "c5a": "C5a 16x16 armadillo_standin grid flattened into one mesh (83.9 M tri, diffuse) 3840x2160 spp4 depth8, camera pulled back",
     "c5b": "C5b one armadillo_standin BLAS x 256 instances (diffuse/refractive alternating) 3840x2160 spp4 depth8, camera pulled back",
+    "c1": "C1 cube_scene.obj(mirror, centre) + cube.obj(diffuse, T(0,0,5)), skybox_texture_sea fixture 256x256, 800x600 spp4 MAX_BOUNCE_COUNT 63 (config.h defaults)",
 }
 CPU_SAMPLE_RAYS = 5.5e6  # the CPU arms render every k-th tile, k chosen so that a step is about this many rays
 
@@ -147,7 +149,7 @@ def cpu_arm(rt, inputs, cam, params, steps, warmup, rays_per_frame, want_image=F
     return rays * len(times) / total / 1e6, 1e3 * total / len(times), cores, sample, rays, img
 
 
-RAYS_PER_FRAME_HINT = {"c3": 49.1e6, "c4": 196.3e6, "c2": 10.4e6, "c5a": 41.7e6, "c5b": 50.2e6}
+RAYS_PER_FRAME_HINT = {"c1": 3.0e6, "c3": 49.1e6, "c4": 196.3e6, "c2": 10.4e6, "c5a": 41.7e6, "c5b": 50.2e6}
 
 
 def source_hash():
@@ -233,7 +235,8 @@ def main():
     wl = args.workload or ("c3" if args.gpus <= 1 else "c4")
     builder, W, H, depth, spp = WORKLOADS[wl]
     config = {"workload": WORKLOAD_TEXT[wl], "width": W, "height": H, "spp": spp, "max_bounce_count": depth,
-              "skybox": f"procedural {args.sky}x{args.sky}x6 RGBA8", "mesh": "armadillo_standin" if wl != "c2" else "teapot",
+              "skybox": f"procedural {args.sky}x{args.sky}x6 RGBA8" if wl != "c1" else "skybox_texture_sea fixture 256x256x6 RGBA8",
+              "mesh": {"c2": "teapot", "c1": "cube_scene"}.get(wl, "armadillo_standin"),
               "l2": "ray-state buffers (GBs per frame) exceed L2; a 512 MiB buffer is also overwritten between steps"}
 
     if args.impl == "reference":

@@ -50,8 +50,9 @@ enum { RT_LOCATION_HOST = 0, RT_LOCATION_DEVICE = 1 };
  * from the same LBVH (Morton sort -> Karras tree -> SAH treelet refinement); they differ in
  * the node layout the traversal kernels read. */
 enum {
-  RT_ACCEL_DEFAULT = 0,   /* the product path: currently RT_ACCEL_BVH2 (fastest measured on
-                             B200)                                   */
+  RT_ACCEL_DEFAULT = 0,   /* the product path, chosen per mesh by measurement:
+                             RT_ACCEL_BVH2, or RT_ACCEL_WIDE4 when nodes + triangles exceed
+                             256 MB (they no longer live in L2)                            */
   RT_ACCEL_BVH2 = 1,      /* binary nodes, two FP32 child boxes, 64 B = 2 x 256-bit loads;
                              ordered traversal                                            */
   RT_ACCEL_BRUTE = 2,     /* no hierarchy: every ray tests every triangle (tiny scenes

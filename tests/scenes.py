@@ -70,6 +70,11 @@ def c1_scene(rt, sky=None):
                           sea_sky_256() if sky is None else sky)
 
 
+def c1_bench_scene(rt, sky_size=None):
+    """C1 for bench.py --workload c1 (the sea-sky fixture whatever sky size the other workloads use)."""
+    return c1_scene(rt)
+
+
 def c1_params(rt):
     """800x600 window (main.cpp:805), MAX_BOUNCE_COUNT 63, SAMPLES_PER_PIXEL 4 (config.h:26-27)."""
     return rt.FrameParams.make(800, 600, 63, 4)

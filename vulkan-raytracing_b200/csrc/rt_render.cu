@@ -609,6 +609,245 @@ __global__ void RT_TRACE_BOUNDS
   }
 }
 
+// ---- the same launch with stragglers set aside (RT_MIGRATE = T > 0) -------------------------------------------------
+// A warp runs its 32 rays to completion, so a batch lasts as long as its longest ray: in bounces >= 3 of C3 40 % of the
+// closest-hit launch's warp instructions execute with 1-3 active lanes (ncu source view) - the last rays of every batch.
+// Here a batch ends when no more than T of its rays are still traversing: those lanes write their traversal state
+// (node, stack, closest hit so far, instance) to a buffer private to the warp and the warp takes the next batch; when
+// the buffer holds a batch's worth (or the queue is empty) the warp resumes those rays together - from where they
+// stopped, nothing is traversed twice.  Long rays so share warps with long rays.  No inter-warp traffic, no votes in
+// the loop: a lane reads one shared-memory word per node visit.  Binary layout, instances looped (no top-level tree).
+constexpr int MIG_STACK = 40;   // deepest stack a ray may have when it is set aside (deeper ones keep running)
+struct __align__(16) MigEntry {
+  uint32_t idx, where, node;     // ray, (instance | stack depth << 8), node to visit next
+  uint32_t b_inst, b_prim;
+  float b_t, b_u, b_v;
+  uint32_t stack[MIG_STACK];
+};
+
+// trace_bvh2_direct with an exit (CUT): returns true when the lane was asked to stop (node and stack say where).  The
+// live count is read beside the node and looked at when the node's boxes have been tested.  Measured: the check costs
+// the loop 20-25 % wherever it is placed (end of the node visit, every 8th visit, only where the stack is popped) and
+// whatever T is - more than setting the stragglers aside returns (profiles/r02_migrate.txt) - so CUT is opt-in.
+template <bool COUNT, bool CUT>
+__device__ __forceinline__ bool trace_bvh2_mig(const BlasDev& b, const RayObj& r, float tmin, uint32_t inst, HitRec& best,
+                                               SlimStack& st, int& node, uint32_t live_addr, int T, TravCounters* cnt) {
+  st.park_ray(r);
+  while (true) {
+    if (node < 0) {
+      test_leaf_tri<false, COUNT>(b, (uint32_t)~node, st.tri_ray(r), tmin, inst, best, cnt);
+      if (st.empty()) break;
+      node = (int)st.pop1();
+      continue;
+    }
+    const float8 lo8 = ldg256(&b.nodes[4 * (size_t)node]), hi8 = ldg256(&b.nodes[4 * (size_t)node + 2]);
+    int lv = 0x7FFFFFFF;
+    if (CUT) asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(lv) : "r"(live_addr));
+    const float4 n0 = lo8.a, n1 = lo8.b, n2 = hi8.a, n3 = hi8.b;
+    if (COUNT) cnt->nodes++;
+    float tn0, tf0, tn1, tf1;
+    RT_SLAB(r, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
+    RT_SLAB(r, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
+    const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+    int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
+    if (h0 && h1) {
+      if (tn1 < tn0) { const int t = c0; c0 = c1; c1 = t; }
+      st.push1((uint32_t)c1);
+      node = c0;
+    } else if (h0) {
+      node = c0;
+    } else if (h1) {
+      node = c1;
+    } else {
+      if (st.empty()) break;
+      node = (int)st.pop1();
+    }
+    if (CUT && lv <= T && st.sp <= MIG_STACK) return true;   // `node` (an inner node or a leaf) is where the ray goes on
+  }
+  return false;
+}
+
+template <bool COUNT, bool CUT>
+__global__ void __launch_bounds__(32, 32)
+    k_trace_shade_mig(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt0, uint32_t bounce, const float4* __restrict__ rayO,
+                      const float4* __restrict__ rayD, float4* __restrict__ nextO, float4* __restrict__ nextD,
+                      float4* __restrict__ shadowQ, float4* __restrict__ sample, rt_hit* __restrict__ primary,
+                      unsigned long long* __restrict__ stats64, MigEntry* __restrict__ mig, int T, int F) {
+  __shared__ uint2 stack_sm[STACK_U2 * 32];
+  __shared__ int s_live, s_nbuf;
+  uint32_t stack_loc[STACK_LOCAL];
+  SlimStack st;
+  st.init(stack_sm, stack_loc);
+  TravCounters tc{0ull, 0ull};
+  MigEntry* my = mig + (size_t)blockIdx.x * 32;
+  // shared-memory address of s_live, made opaque so that it stays in a register (rebuilt from SR_CgaCtaId with an
+  // S2R per node visit otherwise)
+  uint32_t live_addr = (uint32_t)__cvta_generic_to_shared(&s_live);
+  asm volatile("mov.u32 %0, %0;" : "+r"(live_addr));
+  uint32_t* cnt = cnt0 + (size_t)bounce * C_STRIDE;
+  uint32_t* cntNext = cnt + C_STRIDE;
+  const uint32_t n = cnt[C_NRAY];
+  const bool last = bounce >= U.max_bounce;
+  uint32_t n_miss = 0, n_diff = 0, n_spec = 0, n_shadow = 0;
+  bool main_done = false;   // warp-uniform
+  if (lane_id() == 0) s_nbuf = 0;
+  __syncwarp();
+  while (true) {
+    const int nbuf = s_nbuf;   // rays this warp has set aside (uniform: read behind a warp barrier)
+    bool have = false, resumed = false;
+    uint32_t idx = 0;
+    const int room = T * (int)min(scene.n_inst, 8u);   // a batch can set aside up to T rays per instance
+    if (!main_done && nbuf + room <= 32 && nbuf < F) {
+      uint32_t base = 0;
+      if (lane_id() == 0) base = atomicAdd(&cnt[C_WTRACE], 32u);
+      base = __shfl_sync(0xFFFFFFFFu, base, 0);
+      if (base >= n) main_done = true;
+      else { idx = base + lane_id(); have = idx < n; }
+    }
+    int inst_i = 0, node = 0;
+    HitRec best;
+    best.inst = RT_MISS; best.prim = RT_MISS; best.t = u2f(f2u(10000.0f) - 1u); best.u = 0.0f; best.v = 0.0f;
+    st.sp = 0;
+    if (main_done || nbuf + room > 32 || nbuf >= F) {   // resume what was set aside
+      if (nbuf == 0) break;             // (only reached with the queue empty)
+      resumed = true;
+      have = (int)lane_id() < nbuf;
+      if (have) {
+        const MigEntry& e = my[lane_id()];   // (L2 loads: the entry was stored by another lane of this warp)
+        const uint4 h0 = __ldcg((const uint4*)&e), h1 = __ldcg((const uint4*)&e + 1);
+        idx = h0.x;
+        inst_i = (int)(h0.y & 0xFFu);
+        const int sp = (int)(h0.y >> 8);
+        node = (int)h0.z;
+        best.inst = h0.w; best.prim = h1.x; best.t = __uint_as_float(h1.y); best.u = __uint_as_float(h1.z); best.v = __uint_as_float(h1.w);
+        for (int k = 0; k < sp; k++) st.push1(__ldcg(&e.stack[k]));
+      }
+      __syncwarp();
+      if (lane_id() == 0) s_nbuf = 0;
+    }
+    // a batch that nothing can follow (queue empty) runs to completion
+    const int Tnow = main_done ? -1 : T;
+    bool emit = false, cont = false, aside = false;
+    f3 P = mk3(0, 0, 0), N = mk3(0, 0, 0), o = mk3(0, 0, 0), d = mk3(0, 0, 0), dn = mk3(0, 0, 0);
+    uint32_t slot = 0, inst = 0;
+    RayObj rw;
+    rw.o = o; rw.idir = mk3(1, 1, 1);
+    if (have) {
+      const float4 ro = rayO[idx], rd = rayD[idx];
+      slot = __float_as_uint(ro.w);
+      o = mk3(ro.x, ro.y, ro.z);
+      d = mk3(rd.x, rd.y, rd.z);
+      rw.o = o;
+      rw.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
+    }
+    // The instances one after the other, the whole warp in step (a lane that has nothing to do in instance i waits for
+    // the others at the end of the iteration, as it does in trace_scene): s_live counts the lanes traversing instance i.
+    for (uint32_t i = 0; i < scene.n_inst; i++) {
+      const InstDev& in = scene.inst[i];
+      const bool mid = resumed && (int)i == inst_i;   // this lane enters instance i in the middle of its traversal
+      bool go = have && !aside && (int)i >= inst_i;
+      if (go && !mid && scene.n_inst > 1)
+        go = slab_test(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], 0.001f, best.t);
+      const BlasDev b = scene.blas[in.mesh];
+      if (go && b.ntri == 0) go = false;
+      const uint32_t gm = __ballot_sync(0xFFFFFFFFu, go);
+      if (gm == 0u) continue;
+      if (lane_id() == 0) s_live = __popc(gm);
+      __syncwarp();
+      // rays are only set aside where many started together: the last T of them, at most a quarter (a phase that begins
+      // with three lanes has no stragglers, only three rays)
+      const int thr = Tnow < 0 ? -1 : min(Tnow, __popc(gm) >> 2);
+      if (go) {
+        const RayObj r = ray_setup(xform_point(in.w2o, o), xform_vector(in.w2o, d));
+        if (b.ntri == 1) {
+          test_leaf_tri<false, COUNT>(b, 0, r, 0.001f, i, best, &tc);
+        } else {
+          if (!mid) { st.sp = 0; node = 0; }
+          if (trace_bvh2_mig<COUNT, CUT>(b, r, 0.001f, i, best, st, node, live_addr, thr, &tc)) {
+            const int pos = atomicAdd(&s_nbuf, 1);
+            MigEntry& e = my[pos];
+            e.idx = idx;
+            e.where = i | ((uint32_t)st.sp << 8);
+            e.node = (uint32_t)node;
+            e.b_inst = best.inst; e.b_prim = best.prim; e.b_t = best.t; e.b_u = best.u; e.b_v = best.v;
+            const int sp = st.sp;
+            for (int k = 0; k < sp; k++) e.stack[k] = k < STACK_SM ? st.sm[k * 32] : st.loc[k - STACK_SM];
+            aside = true;
+          }
+        }
+        atomicSub(&s_live, 1);
+      }
+      __syncwarp();
+    }
+    if (have) {
+      if (!aside) {
+        const bool hit = best.inst != RT_MISS;
+        if (primary) {
+          uint32_t x, y;
+          slot_to_pixel(U, slot / U.spp, x, y);
+          rt_hit out;
+          out.instance = best.inst; out.primitive = best.prim; out.t = hit ? best.t : 0.0f; out.u = best.u; out.v = best.v;
+          primary[((size_t)y * U.width + x) * U.spp + (slot % U.spp)] = out;
+        }
+        if (!hit) {
+          const f3 c = sky_sample(scene, mk3(d.x, d.y, -d.z));
+          sample[slot] = make_float4(c.x, c.y, c.z, 1.0f);
+          n_miss++;
+        } else {
+          inst = best.inst;
+          rchit(scene, best.inst, best.prim, best.u, best.v, P, N);
+          const uint32_t type = scene.inst[best.inst].type;
+          if (type == 0u) {
+            n_diff++;
+            emit = !(dot3(d, N) >= 0.0f);
+            if (emit && scene.mat) {
+              const f3 amb = material_ambient(scene.mat[inst]);
+              sample[slot] = make_float4(amb.x, amb.y, amb.z, 1.0f);
+            }
+          } else {
+            n_spec++;
+            if (!last) {
+              dn = d;
+              scatter(type, P, N, o, dn, scene.mat ? scene.mat[inst].ni : 1.52f);
+              cont = true;
+            }
+          }
+        }
+      }
+    }
+    uint32_t dst = warp_append(emit, &cnt0[C_SHCUR]);
+    if (emit) {
+      n_shadow++;
+      shadowQ[3 * (size_t)dst + 0] = make_float4(P.x, P.y, P.z, __uint_as_float(slot));
+      shadowQ[3 * (size_t)dst + 1] = make_float4(N.x, N.y, N.z, __uint_as_float(inst));
+      shadowQ[3 * (size_t)dst + 2] = make_float4(d.x, d.y, d.z, 0.0f);
+    }
+    dst = warp_append(cont, &cntNext[C_NRAY]);
+    if (cont) {
+      nextO[dst] = make_float4(o.x, o.y, o.z, __uint_as_float(slot));
+      nextD[dst] = make_float4(dn.x, dn.y, dn.z, 0.0f);
+    }
+    __syncwarp();   // s_nbuf and the entries written by this batch are visible to the whole warp
+  }
+#pragma unroll
+  for (int k = 16; k > 0; k >>= 1) {
+    n_miss += __shfl_xor_sync(0xFFFFFFFFu, n_miss, k);
+    n_diff += __shfl_xor_sync(0xFFFFFFFFu, n_diff, k);
+    n_spec += __shfl_xor_sync(0xFFFFFFFFu, n_spec, k);
+    n_shadow += __shfl_xor_sync(0xFFFFFFFFu, n_shadow, k);
+  }
+  if (lane_id() == 0) {
+    if (n_miss) atomicAdd(&cnt[C_NMISS], n_miss);
+    if (n_diff) atomicAdd(&cnt[C_NDIFF], n_diff);
+    if (n_spec) atomicAdd(&cnt[C_NSPEC], n_spec);
+    if (n_shadow) atomicAdd(&cnt[C_NSHADOW], n_shadow);
+  }
+  if (COUNT) {
+    atomicAdd(&stats64[0], tc.nodes);
+    atomicAdd(&stats64[1], tc.tris);
+  }
+}
+
 }  // namespace rt
 #include "rt_path.cuh"   // the bounce-fused path kernel (uses lit_color, warp helpers, the counter slots)
 namespace rt {
@@ -872,7 +1111,8 @@ __global__ void __launch_bounds__(TRACE_THREADS)
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-static const int RT_MAX_SUB = 4;
+static const int RT_MAX_SUB = 8;
+struct MigEntry;
 struct FramePipeline {
   size_t cap = 0;  // ray slots the buffers hold
   float4 *rayO[2] = {nullptr, nullptr}, *rayD[2] = {nullptr, nullptr};
@@ -900,6 +1140,8 @@ struct FramePipeline {
     size_t alive_cap = 0;
     cudaEvent_t done = nullptr;
   } sub[RT_MAX_SUB];
+  MigEntry* mig = nullptr;       // k_trace_shade_mig: 32 entries per resident warp and sub-frame
+  size_t mig_blocks = 0;
   // early resolve of the tiles k_raygen finished
   uint32_t* tile_live = nullptr;
   size_t tile_cap = 0;
@@ -944,6 +1186,7 @@ void pipeline_destroy(FramePipeline* p) {
   }
   if (p->start) cudaEventDestroy(p->start);
   cudaFree(p->tile_live);
+  cudaFree(p->mig);
   for (auto& e : p->early_st) if (e) cudaStreamDestroy(e);
   for (auto& e : p->ray_done) if (e) cudaEventDestroy(e);
   for (auto& e : p->early_done) if (e) cudaEventDestroy(e);
@@ -1107,6 +1350,22 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   // back between the traversal launches.  Ray reordering and the warp-synchronous 8-wide variant keep the separate kernels.
   static const bool fuse_shade_env = getenv("RT_FUSE_SHADE") ? atoi(getenv("RT_FUSE_SHADE")) != 0 : true;
   const bool fuse_shade = fuse_shade_env && !may_sort && !(accel == ACCEL_WIDE && wave_on && rq.scene.tlas == nullptr);
+  // RT_MIGRATE = T: a batch of the closest-hit launch ends when no more than T of its rays are still traversing; the
+  // stragglers are set aside with their traversal state and resumed together (k_trace_shade_mig)
+  static const int migrate_F = getenv("RT_MIGRATE_FLUSH") ? std::max(1, atoi(getenv("RT_MIGRATE_FLUSH"))) : 32;   // resume when this many are set aside
+  static const int migrate_env = getenv("RT_MIGRATE") ? std::max(0, std::min(16, atoi(getenv("RT_MIGRATE")))) : 0;
+  // Binary layout, instances looped: the closest-hit launch takes the instances one after the other with the whole warp in
+  // step (k_trace_shade_mig<., false>: an instance no lane reaches is skipped by one vote, the lanes meet again after
+  // each instance): C3 8.48 -> 8.31 ms, a 1/8 shard of C4 4.38 -> 4.28.  RT_INSTANCE_STEP=0: the generic k_trace_shade.
+  static const bool step_env = getenv("RT_INSTANCE_STEP") ? atoi(getenv("RT_INSTANCE_STEP")) != 0 : true;
+  const bool steppable = fuse_shade && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && rq.scene.n_inst <= 4u && RT_TRACE_THREADS == 32;
+  const bool stepped = step_env && steppable;
+  const bool migrate = migrate_env > 0 && steppable;
+  const int migrate_T = migrate ? std::min(migrate_env, 16 / (int)std::max(1u, rq.scene.n_inst)) : 0;   // the buffer holds 32
+  if (migrate && !p->mig) {
+    p->mig_blocks = (size_t)std::min(persistent_blocks(k_trace_shade_mig<false, true>, 32), persistent_blocks(k_trace_shade_mig<true, true>, 32));
+    RT_CUDA_TRY(cudaMalloc(&p->mig, (size_t)RT_MAX_SUB * p->mig_blocks * 32 * sizeof(MigEntry)), err);
+  }
   const bool fused = fused_env && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && !may_sort && rq.scene.n_inst <= 32u;
   const int nsub = (sub_env >= 2 && nslots >= sub_min_slots && !may_sort && !wave)
                        ? (int)std::min<uint32_t>((uint32_t)std::min(sub_env, RT_MAX_SUB), U.n_local_tiles) : 1;
@@ -1275,6 +1534,20 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j); \
   }
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 0], cs), err);
+#define CALL_STEPPED(C, CUT, BLOCKS, MG, T)                                                                                   \
+  k_trace_shade_mig<C, CUT><<<BLOCKS, 32, 0, cs>>>(rq.scene, U, c.cnt, j, c.rayO[cur], c.rayD[cur], c.rayO[cur ^ 1], c.rayD[cur ^ 1], \
+                                                   c.shadowQ, p->sample, prim, p->stats64, MG, T, migrate_F)
+    if (migrate) {
+      MigEntry* mg = p->mig + (size_t)(&c - ctx) * p->mig_blocks * 32;
+      if (counting) CALL_STEPPED(true, true, (int)p->mig_blocks, mg, migrate_T);
+      else CALL_STEPPED(false, true, (int)p->mig_blocks, mg, migrate_T);
+    } else if (stepped) {
+      static int sb_blocks[2] = {0, 0};
+      if (!sb_blocks[0]) { sb_blocks[0] = persistent_blocks(k_trace_shade_mig<false, false>, 32); sb_blocks[1] = persistent_blocks(k_trace_shade_mig<true, false>, 32); }
+      if (counting) CALL_STEPPED(true, false, sb_blocks[1], nullptr, 0);
+      else CALL_STEPPED(false, false, sb_blocks[0], nullptr, 0);
+    } else
+#undef CALL_STEPPED
     RT_DISPATCH_ACCEL(accel, counting, CALL_TRACE_SHADE);
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 1], cs), err);
     if (shadow_async) {
@@ -1332,6 +1605,21 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   // RT_FUSE_FROM = j: bounces < j run as wavefront launches (coherent rays, full batches), the rest of
   // every path in the fused kernel
   static const uint32_t fuse_from = getenv("RT_FUSE_FROM") ? (uint32_t)atoi(getenv("RT_FUSE_FROM")) : 0u;
+  // RT_STAGGER = b: the sub-frames are started one after the other - sub-frame k traces its primary rays when sub-frame
+  // k - 1 has finished bounce b - so that the thin late bounces of one sub-frame run beside the full early bounces of the next
+  static const int stagger = getenv("RT_STAGGER") ? atoi(getenv("RT_STAGGER")) : -1;
+  if (stagger >= 0 && fuse_shade && !fused && nsub > 1) {
+    for (int k = 0; k < nsub; k++) {
+      if (k > 0) {
+        const uint32_t b = std::min<uint32_t>((uint32_t)stagger, ctx[k - 1].last_bounce);
+        RT_CUDA_TRY(cudaStreamWaitEvent(ctx[k].st, ctx[k - 1].sb->kev[4 * b + 1], 0), err);
+      }
+      for (uint32_t j = 0; j <= U.max_bounce && !ctx[k].dead; j++) {
+        rc = enqueue_bounce_fused(ctx[k], j);
+        if (rc != RT_OK) return rc;
+      }
+    }
+  } else
   for (uint32_t j = 0; j <= U.max_bounce; j++) {
     if (fused && j >= fuse_from) {
       for (int k = 0; k < nsub; k++) {

@@ -742,7 +742,36 @@ __global__ void __launch_bounds__(32, 32)
     }
     // The instances one after the other, the whole warp in step (a lane that has nothing to do in instance i waits for
     // the others at the end of the iteration, as it does in trace_scene): s_live counts the lanes traversing instance i.
-    for (uint32_t i = 0; i < scene.n_inst; i++) {
+    // Order of the instances for this batch: nearest first for the warp as a whole (mean distance at which its rays enter
+    // the instance's world box), so that the hit found in the nearer instance culls the box of the farther one.  The order
+    // only steers the search: the closest hit with the (instance, primitive) tie rule does not depend on it.
+    uint32_t order = 0x3210u;   // 4 bits per position
+    if (!CUT && scene.n_inst > 1) {
+      float key[4] = {3.0e38f, 3.0e38f, 3.0e38f, 3.0e38f};
+#pragma unroll
+      for (uint32_t i = 0; i < 4; i++) {
+        if (i >= scene.n_inst) break;
+        const InstDev& in = scene.inst[i];
+        float tn = 0.0f, tf = -1.0f;
+        if (have) slab_interval(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], 0.001f, 10000.0f, tn, tf);
+        const bool h = have && tn <= tf;
+        float sum = h ? tn : 0.0f;
+        uint32_t c = h ? 1u : 0u;
+#pragma unroll
+        for (int k = 16; k > 0; k >>= 1) { sum += __shfl_xor_sync(0xFFFFFFFFu, sum, k); c += __shfl_xor_sync(0xFFFFFFFFu, c, k); }
+        key[i] = c ? sum / (float)c : 3.0e38f;
+      }
+      // (xor-butterfly sums are the same in every lane: the order is warp-uniform)
+      uint32_t id[4] = {0u, 1u, 2u, 3u};
+#pragma unroll
+      for (int a = 1; a < 4; a++)
+#pragma unroll
+        for (int bq = a; bq > 0; bq--)
+          if (key[bq] < key[bq - 1]) { const float tk = key[bq]; key[bq] = key[bq - 1]; key[bq - 1] = tk; const uint32_t ti = id[bq]; id[bq] = id[bq - 1]; id[bq - 1] = ti; }
+      order = id[0] | (id[1] << 4) | (id[2] << 8) | (id[3] << 12);
+    }
+    for (uint32_t oi = 0; oi < scene.n_inst; oi++) {
+      const uint32_t i = CUT ? oi : ((order >> (4 * oi)) & 0xFu);
       const InstDev& in = scene.inst[i];
       const bool mid = resumed && (int)i == inst_i;   // this lane enters instance i in the middle of its traversal
       bool go = have && !aside && (int)i >= inst_i;

@@ -702,6 +702,7 @@ print('PARITY OK', sc.stats()['kernel_launches'])
     {"RT_MIGRATE": "4"},                                 # stragglers of a batch set aside with their traversal state, resumed together
     {"RT_MIGRATE": "12", "RT_SUBFRAMES": "1"},
     {"RT_MIGRATE": "1", "RT_SUBFRAMES": "3", "RT_SUBFRAMES_MIN": "1"},
+    {"RT_SHADOW_STEP": "1"},                             # shadow rays through looped instances with the warp in step
     {"RT_INSTANCE_STEP": "0"},                           # the generic closest-hit + shading launch (trace_scene) for looped instances
     {"RT_FUSE_SHADE": "0"},                              # separate shading kernels between the traversal launches (round 1)
     {"RT_FUSE_SHADE": "0", "RT_SHADOW_STREAM": "0", "RT_SUBFRAMES": "1"},

@@ -457,6 +457,63 @@ struct ShadowSink {
   }
 };
 
+// trace_scene for looped instances (no top-level tree, <= 4 instances), called by the WHOLE warp: the instances are
+// taken one after the other with the warp in step - an instance no lane's ray reaches is skipped by one vote, the lanes
+// meet again after every instance - and nearest first for the warp as a whole (mean distance at which its rays enter the
+// instance's world box), so that a hit in the nearer instance culls the box of the farther one.  Per-lane loops over the
+// instances let the lanes of a warp drift into different instances, which then run the same traversal code one after the
+// other (profiles/r02_migrate.txt).  The order only steers the search: closest hit = smallest t with the (instance,
+// primitive) tie rule, any-hit = a boolean.
+template <int ACCEL, bool ANY, bool COUNT>
+__device__ __forceinline__ bool trace_scene_stepped(const SceneDev& s, bool have, f3 o, f3 d, float tmin, float tmax, HitRec& best,
+                                                    typename StackFor<ACCEL>::type& st, TravCounters* cnt) {
+  typedef typename StackFor<ACCEL>::type Stack;
+  SceneDev sc = s;
+  sc.accel = ACCEL;
+  best.inst = RT_MISS; best.prim = RT_MISS; best.t = u2f(f2u(tmax) - 1u); best.u = 0.0f; best.v = 0.0f;
+  RayObj rw;
+  rw.o = o;
+  rw.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
+  uint32_t order = 0x3210u;
+  if (s.n_inst > 1) {
+    float key[4] = {3.0e38f, 3.0e38f, 3.0e38f, 3.0e38f};
+#pragma unroll
+    for (uint32_t i = 0; i < 4; i++) {
+      if (i >= s.n_inst) break;
+      const InstDev& in = s.inst[i];
+      float tn = 0.0f, tf = -1.0f;
+      if (have) slab_interval(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], tmin, tmax, tn, tf);
+      const bool h = have && tn <= tf;
+      float sum = h ? tn : 0.0f;
+      uint32_t c = h ? 1u : 0u;
+#pragma unroll
+      for (int k = 16; k > 0; k >>= 1) { sum += __shfl_xor_sync(0xFFFFFFFFu, sum, k); c += __shfl_xor_sync(0xFFFFFFFFu, c, k); }
+      key[i] = c ? sum / (float)c : 3.0e38f;
+    }
+    uint32_t id[4] = {0u, 1u, 2u, 3u};
+#pragma unroll
+    for (int a = 1; a < 4; a++)
+#pragma unroll
+      for (int bq = a; bq > 0; bq--)
+        if (key[bq] < key[bq - 1]) { const float tk = key[bq]; key[bq] = key[bq - 1]; key[bq - 1] = tk; const uint32_t ti = id[bq]; id[bq] = id[bq - 1]; id[bq - 1] = ti; }
+    order = id[0] | (id[1] << 4) | (id[2] << 8) | (id[3] << 12);
+  }
+  bool found = false;   // ANY: an occluder was hit
+  for (uint32_t oi = 0; oi < s.n_inst; oi++) {
+    const uint32_t i = (order >> (4 * oi)) & 0xFu;
+    const InstDev& in = s.inst[i];
+    bool go = have && !found;
+    if (go && s.n_inst > 1) go = slab_test(rw, in.wlo[0], in.wlo[1], in.wlo[2], in.whi[0], in.whi[1], in.whi[2], tmin, best.t);
+    if (!__any_sync(0xFFFFFFFFu, go)) continue;
+    if (go) {
+      const bool hit = trace_instance<Stack, ANY, COUNT>(sc, i, o, d, rw, false, tmin, best, st, cnt);
+      if (ANY && hit) found = true;
+    }
+    __syncwarp();
+  }
+  return ANY ? found : best.inst != RT_MISS;
+}
+
 template <int ACCEL, bool COUNT>
 __global__ void RT_TRACE_BOUNDS
     k_shadow(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
@@ -470,6 +527,8 @@ __global__ void RT_TRACE_BOUNDS
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NSHADOW];
   if (n == 0u) return;
+  const bool stepped = (bounce >> 31) != 0u;   // host flag in the top bit
+  bounce &= 0x7FFFFFFFu;
   if (cnt0) {   // append-only queue (k_trace_shade): this bounce's rays start behind those of the earlier bounces
     uint32_t start = 0;
     for (uint32_t j = 0; j < bounce; j++) start += cnt0[(size_t)j * C_STRIDE + C_NSHADOW];
@@ -481,7 +540,22 @@ __global__ void RT_TRACE_BOUNDS
     base = __shfl_sync(0xFFFFFFFFu, base, 0);
     if (base >= n) break;
     const uint32_t i = base + lane_id();
-    if (i < n) {
+    if (stepped) {   // looped instances: the warp takes them in step (trace_scene_stepped)
+      const bool have = i < n;
+      float4 q0 = make_float4(0, 0, 0, 0), q1 = make_float4(0, 0, 1, 0), q2 = make_float4(0, 0, 1, 0);
+      if (have) { q0 = shadowQ[3 * (size_t)i]; q1 = shadowQ[3 * (size_t)i + 1]; q2 = shadowQ[3 * (size_t)i + 2]; }
+      const f3 P = mk3(q0.x, q0.y, q0.z), N = mk3(q1.x, q1.y, q1.z), d = mk3(q2.x, q2.y, q2.z);
+      const uint32_t s = __float_as_uint(q0.w);
+      f3 so, L;
+      float dist;
+      shadow_ray(U, P, N, so, L, dist);
+      HitRec h;
+      const bool occluded = trace_scene_stepped<ACCEL, true, COUNT>(scene, have, so, L, 0.001f, dist, h, st, &tc);
+      if (have && !occluded) {
+        const f3 c = lit_color(scene, U, q1.w, d, N, L, s % U.spp);
+        sample[s] = make_float4(c.x, c.y, c.z, 1.0f);
+      }
+    } else if (i < n) {
       const float4 q0 = shadowQ[3 * (size_t)i], q1 = shadowQ[3 * (size_t)i + 1], q2 = shadowQ[3 * (size_t)i + 2];
       const f3 P = mk3(q0.x, q0.y, q0.z), N = mk3(q1.x, q1.y, q1.z), d = mk3(q2.x, q2.y, q2.z);
       const uint32_t s = __float_as_uint(q0.w);
@@ -1389,6 +1463,10 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   static const bool step_env = getenv("RT_INSTANCE_STEP") ? atoi(getenv("RT_INSTANCE_STEP")) != 0 : true;
   const bool steppable = fuse_shade && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && rq.scene.n_inst <= 4u && RT_TRACE_THREADS == 32;
   const bool stepped = step_env && steppable;
+  // RT_SHADOW_STEP=1: the shadow launch steps through looped instances too (any layout).  Off: measured slower
+  // (C3 7.78 -> 7.95 ms; the any-hit traversal parks leaves by votes of its own and gains nothing from the order)
+  static const bool shadow_step_env = getenv("RT_SHADOW_STEP") ? atoi(getenv("RT_SHADOW_STEP")) != 0 : false;
+  const uint32_t shadow_step_flag = (shadow_step_env && rq.scene.tlas == nullptr && rq.scene.n_inst <= 4u && rq.scene.n_inst > 1u && !wave) ? 0x80000000u : 0u;
   const bool migrate = migrate_env > 0 && steppable;
   const int migrate_T = migrate ? std::min(migrate_env, 16 / (int)std::max(1u, rq.scene.n_inst)) : 0;   // the buffer holds 32
   if (migrate && !p->mig) {
@@ -1499,7 +1577,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   {                                                                                                       \
     static int blocks = 0;                                                                                \
     if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
-    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j); \
+    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j | shadow_step_flag); \
   }
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 2], sst), err);
     if (wave) {
@@ -1560,7 +1638,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   {                                                                                                       \
     static int blocks = 0;                                                                                \
     if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
-    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j); \
+    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j | shadow_step_flag); \
   }
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 0], cs), err);
 #define CALL_STEPPED(C, CUT, BLOCKS, MG, T)                                                                                   \

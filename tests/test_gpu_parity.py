@@ -684,6 +684,7 @@ A = int(os.environ.get('TEST_ACCEL', '0'))
 t.check_frame(rt, ob, scenes.smoke_scene(rt), rt.FrameParams.make(160, 120, 6, 4), A)
 t.check_frame(rt, ob, scenes.c3_scene(rt, level=5, sky_size=256), rt.FrameParams.make(384, 216, 8, 4), A)
 t.check_frame(rt, ob, scenes.c1_like_scene(rt), rt.FrameParams.make(203, 151, 63, 4), A)
+t.check_frame(rt, ob, scenes.instanced_grid_scene(rt), rt.FrameParams.make(240, 160, 5, 4), A)     # 13 instances: top-level tree
 sc = rt.Scene(scenes.c3_scene(rt, level=6, sky_size=128), device_id=0, accel=A)
 p = rt.FrameParams.make(2048, 1600, 8, 4)          # 13.1 M sample slots: above the two-sub-frame threshold
 img = sc.render(rt.CameraVectors.default(), p)
@@ -702,6 +703,7 @@ print('PARITY OK', sc.stats()['kernel_launches'])
     {"RT_MIGRATE": "4"},                                 # stragglers of a batch set aside with their traversal state, resumed together
     {"RT_MIGRATE": "12", "RT_SUBFRAMES": "1"},
     {"RT_MIGRATE": "1", "RT_SUBFRAMES": "3", "RT_SUBFRAMES_MIN": "1"},
+    {"RT_TLAS_STEP": "0", "RT_SHADOW_TLAS_STEP": "0"},   # top-level tree walked per lane (trace_scene) instead of with the warp in step
     {"RT_SHADOW_STEP": "1"},                             # shadow rays through looped instances with the warp in step
     {"RT_INSTANCE_STEP": "0"},                           # the generic closest-hit + shading launch (trace_scene) for looped instances
     {"RT_FUSE_SHADE": "0"},                              # separate shading kernels between the traversal launches (round 1)

@@ -514,7 +514,63 @@ __device__ __forceinline__ bool trace_scene_stepped(const SceneDev& s, bool have
   return ANY ? found : best.inst != RT_MISS;
 }
 
-template <int ACCEL, bool COUNT>
+// The same for a scene with a top-level tree, called by the WHOLE warp.  A lane walks the top-level tree (nearest child
+// first, as trace_scene does) only until it reaches an instance; then the warp meets, and all lanes that hold an instance
+// traverse theirs together - different instances, the same traversal code in step.  In trace_scene a lane enters its
+// instance the moment it reaches it, so at any time the lanes of a warp are spread over the top-level walk and the
+// instance traversals at different depths of the call, and those run one after the other.
+template <int ACCEL, bool ANY, bool COUNT>
+__device__ __forceinline__ bool trace_scene_tlas_stepped(const SceneDev& s, bool have, f3 o, f3 d, float tmin, float tmax, HitRec& best,
+                                                         typename StackFor<ACCEL>::type& st, TravCounters* cnt) {
+  typedef typename StackFor<ACCEL>::type Stack;
+  SceneDev sc = s;
+  sc.accel = ACCEL;
+  best.inst = RT_MISS; best.prim = RT_MISS; best.t = u2f(f2u(tmax) - 1u); best.u = 0.0f; best.v = 0.0f;
+  RayObj rw;
+  rw.o = o;
+  rw.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
+  int tstack[RT_MAX_TLAS_DEPTH];
+  int tsp = 0, node = 0;
+  bool walking = have;   // the lane's top-level walk is not finished
+  while (true) {
+    // ---- top level: until this lane stands on an instance (node < 0) or has nothing left
+    while (walking && node >= 0) {
+      const float8 lo8 = ldg256(&s.tlas[4 * (size_t)node]), hi8 = ldg256(&s.tlas[4 * (size_t)node + 2]);
+      const float4 n0 = lo8.a, n1 = lo8.b, n2 = hi8.a, n3 = hi8.b;
+      float tn0, tf0, tn1, tf1;
+      slab_interval(rw, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, tmin, best.t, tn0, tf0);
+      slab_interval(rw, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, tmin, best.t, tn1, tf1);
+      const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+      int c0 = (int)f2u(n3.x), c1 = (int)f2u(n3.y);
+      if (h0 && h1) {
+        if (tn1 < tn0) { const int t = c0; c0 = c1; c1 = t; }
+        if (tsp < RT_MAX_TLAS_DEPTH) tstack[tsp++] = c1;
+        else RT_FLAG_OVERFLOW();
+        node = c0;
+      } else if (h0) {
+        node = c0;
+      } else if (h1) {
+        node = c1;
+      } else if (tsp > 0) {
+        node = tstack[--tsp];
+      } else {
+        walking = false;
+      }
+    }
+    if (!__any_sync(0xFFFFFFFFu, walking)) break;
+    // ---- the instances the lanes stand on, together
+    if (walking) {
+      const bool hit = trace_instance<Stack, ANY, COUNT>(sc, (uint32_t)~node, o, d, rw, false, tmin, best, st, cnt);
+      if (ANY && hit) { walking = false; }
+      else if (tsp > 0) node = tstack[--tsp];
+      else walking = false;
+    }
+    __syncwarp();
+  }
+  return best.inst != RT_MISS;
+}
+
+template <int ACCEL, bool COUNT, bool STEP>
 __global__ void RT_TRACE_BOUNDS
     k_shadow(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt, const float4* __restrict__ shadowQ,
              float4* __restrict__ sample, unsigned long long* __restrict__ stats64, const uint32_t* __restrict__ cnt0,
@@ -527,8 +583,7 @@ __global__ void RT_TRACE_BOUNDS
   TravCounters tc{0ull, 0ull};
   const uint32_t n = cnt[C_NSHADOW];
   if (n == 0u) return;
-  const bool stepped = (bounce >> 31) != 0u;   // host flag in the top bit
-  bounce &= 0x7FFFFFFFu;
+  const bool stepped = STEP;
   if (cnt0) {   // append-only queue (k_trace_shade): this bounce's rays start behind those of the earlier bounces
     uint32_t start = 0;
     for (uint32_t j = 0; j < bounce; j++) start += cnt0[(size_t)j * C_STRIDE + C_NSHADOW];
@@ -550,7 +605,8 @@ __global__ void RT_TRACE_BOUNDS
       float dist;
       shadow_ray(U, P, N, so, L, dist);
       HitRec h;
-      const bool occluded = trace_scene_stepped<ACCEL, true, COUNT>(scene, have, so, L, 0.001f, dist, h, st, &tc);
+      const bool occluded = scene.tlas ? trace_scene_tlas_stepped<ACCEL, true, COUNT>(scene, have, so, L, 0.001f, dist, h, st, &tc)
+                                       : trace_scene_stepped<ACCEL, true, COUNT>(scene, have, so, L, 0.001f, dist, h, st, &tc);
       if (have && !occluded) {
         const f3 c = lit_color(scene, U, q1.w, d, N, L, s % U.spp);
         sample[s] = make_float4(c.x, c.y, c.z, 1.0f);
@@ -586,7 +642,7 @@ __global__ void RT_TRACE_BOUNDS
 // launches of a sub-frame in bounces >= 3, where the frame is a chain of short launches (profiles/r02_fused_shade.txt).
 // Shadow rays are appended to a queue that only grows during the frame (every path emits at most one): the shadow
 // launch of bounce j reads its part while bounce j + 1 already appends behind it, so nothing waits for a shadow launch.
-template <int ACCEL, bool COUNT>
+template <int ACCEL, bool COUNT, bool TLAS>
 __global__ void RT_TRACE_BOUNDS
     k_trace_shade(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt0, uint32_t bounce, const float4* __restrict__ rayO,
                   const float4* __restrict__ rayD, float4* __restrict__ nextO, float4* __restrict__ nextD,
@@ -612,13 +668,19 @@ __global__ void RT_TRACE_BOUNDS
     bool emit = false, cont = false;
     f3 P = mk3(0, 0, 0), N = mk3(0, 0, 0), o = mk3(0, 0, 0), d = mk3(0, 0, 0), dn = mk3(0, 0, 0);
     uint32_t slot = 0, inst = 0;
-    if (idx < n) {
+    const bool have = idx < n;
+    HitRec h;
+    bool hit = false;
+    if (have) {
       const float4 ro = rayO[idx], rd = rayD[idx];
       slot = __float_as_uint(ro.w);
       o = mk3(ro.x, ro.y, ro.z);
       d = mk3(rd.x, rd.y, rd.z);
-      HitRec h;
-      const bool hit = trace_scene_t<ACCEL, false, COUNT>(scene, o, d, 0.001f, 10000.0f, h, st, &tc);   // shader.rgen:86-87
+    }
+    // shader.rgen:86-87.  (TLAS: scene with a top-level tree, traversed with the warp in step)
+    if (TLAS) hit = trace_scene_tlas_stepped<ACCEL, false, COUNT>(scene, have, o, d, 0.001f, 10000.0f, h, st, &tc);
+    else if (have) hit = trace_scene_t<ACCEL, false, COUNT>(scene, o, d, 0.001f, 10000.0f, h, st, &tc);
+    if (have) {
       if (primary) {
         uint32_t x, y;
         slot_to_pixel(U, slot / U.spp, x, y);
@@ -1463,10 +1525,15 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   static const bool step_env = getenv("RT_INSTANCE_STEP") ? atoi(getenv("RT_INSTANCE_STEP")) != 0 : true;
   const bool steppable = fuse_shade && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && rq.scene.n_inst <= 4u && RT_TRACE_THREADS == 32;
   const bool stepped = step_env && steppable;
+  // RT_TLAS_STEP: scenes with a top-level tree - the warp meets between the top-level walk and the instance traversals
+  static const bool tlas_step_env = getenv("RT_TLAS_STEP") ? atoi(getenv("RT_TLAS_STEP")) != 0 : true;
+  const bool tlas_step = tlas_step_env && rq.scene.tlas != nullptr;
   // RT_SHADOW_STEP=1: the shadow launch steps through looped instances too (any layout).  Off: measured slower
   // (C3 7.78 -> 7.95 ms; the any-hit traversal parks leaves by votes of its own and gains nothing from the order)
   static const bool shadow_step_env = getenv("RT_SHADOW_STEP") ? atoi(getenv("RT_SHADOW_STEP")) != 0 : false;
-  const uint32_t shadow_step_flag = (shadow_step_env && rq.scene.tlas == nullptr && rq.scene.n_inst <= 4u && rq.scene.n_inst > 1u && !wave) ? 0x80000000u : 0u;
+  static const bool shadow_tlas_env = getenv("RT_SHADOW_TLAS_STEP") ? atoi(getenv("RT_SHADOW_TLAS_STEP")) != 0 : true;
+  const bool shadow_step = !wave && ((shadow_step_env && rq.scene.tlas == nullptr && rq.scene.n_inst <= 4u && rq.scene.n_inst > 1u) ||
+                                     (shadow_tlas_env && rq.scene.tlas != nullptr));
   const bool migrate = migrate_env > 0 && steppable;
   const int migrate_T = migrate ? std::min(migrate_env, 16 / (int)std::max(1u, rq.scene.n_inst)) : 0;   // the buffer holds 32
   if (migrate && !p->mig) {
@@ -1576,8 +1643,9 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
 #define CALL_SHADOW(A, C)                                                                                 \
   {                                                                                                       \
     static int blocks = 0;                                                                                \
-    if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
-    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j | shadow_step_flag); \
+    if (!blocks) blocks = std::min(persistent_blocks(k_shadow<A, C, false>, TRACE_THREADS), persistent_blocks(k_shadow<A, C, true>, TRACE_THREADS)); \
+    if (shadow_step) k_shadow<A, C, true><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j); \
+    else k_shadow<A, C, false><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j); \
   }
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 2], sst), err);
     if (wave) {
@@ -1629,16 +1697,20 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     const uint32_t* sh_cnt0 = c.cnt;
 #define CALL_TRACE_SHADE(A, C)                                                                                        \
   {                                                                                                                   \
-    static int blocks = 0;                                                                                            \
-    if (!blocks) blocks = persistent_blocks(k_trace_shade<A, C>, TRACE_THREADS);                                      \
-    k_trace_shade<A, C><<<blocks, TRACE_THREADS, 0, cs>>>(rq.scene, U, c.cnt, j, c.rayO[cur], c.rayD[cur], c.rayO[cur ^ 1], \
+    static int blocks[2] = {0, 0};                                                                                    \
+    if (!blocks[0]) { blocks[0] = persistent_blocks(k_trace_shade<A, C, false>, TRACE_THREADS);                       \
+                      blocks[1] = persistent_blocks(k_trace_shade<A, C, true>, TRACE_THREADS); }                      \
+    if (tlas_step) k_trace_shade<A, C, true><<<blocks[1], TRACE_THREADS, 0, cs>>>(rq.scene, U, c.cnt, j, c.rayO[cur], c.rayD[cur], c.rayO[cur ^ 1], \
+                                                          c.rayD[cur ^ 1], c.shadowQ, p->sample, prim, p->stats64);    \
+    else k_trace_shade<A, C, false><<<blocks[0], TRACE_THREADS, 0, cs>>>(rq.scene, U, c.cnt, j, c.rayO[cur], c.rayD[cur], c.rayO[cur ^ 1], \
                                                           c.rayD[cur ^ 1], c.shadowQ, p->sample, prim, p->stats64);    \
   }
 #define CALL_SHADOW_F(A, C)                                                                               \
   {                                                                                                       \
     static int blocks = 0;                                                                                \
-    if (!blocks) blocks = persistent_blocks(k_shadow<A, C>, TRACE_THREADS);                               \
-    k_shadow<A, C><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j | shadow_step_flag); \
+    if (!blocks) blocks = std::min(persistent_blocks(k_shadow<A, C, false>, TRACE_THREADS), persistent_blocks(k_shadow<A, C, true>, TRACE_THREADS)); \
+    if (shadow_step) k_shadow<A, C, true><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j); \
+    else k_shadow<A, C, false><<<blocks, TRACE_THREADS, 0, sst>>>(rq.scene, U, cj, c.shadowQ, p->sample, p->stats64, sh_cnt0, j); \
   }
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 0], cs), err);
 #define CALL_STEPPED(C, CUT, BLOCKS, MG, T)                                                                                   \

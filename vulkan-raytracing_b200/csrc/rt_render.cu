@@ -745,14 +745,20 @@ __global__ void RT_TRACE_BOUNDS
   }
 }
 
-// ---- the same launch with stragglers set aside (RT_MIGRATE = T > 0) -------------------------------------------------
-// A warp runs its 32 rays to completion, so a batch lasts as long as its longest ray: in bounces >= 3 of C3 40 % of the
-// closest-hit launch's warp instructions execute with 1-3 active lanes (ncu source view) - the last rays of every batch.
-// Here a batch ends when no more than T of its rays are still traversing: those lanes write their traversal state
-// (node, stack, closest hit so far, instance) to a buffer private to the warp and the warp takes the next batch; when
-// the buffer holds a batch's worth (or the queue is empty) the warp resumes those rays together - from where they
-// stopped, nothing is traversed twice.  Long rays so share warps with long rays.  No inter-warp traffic, no votes in
-// the loop: a lane reads one shared-memory word per node visit.  Binary layout, instances looped (no top-level tree).
+// ---- closest hit + shading for looped instances, the warp in step (k_trace_shade_step; default for the binary layout) ----
+// Same work as k_trace_shade; two differences in how the warp goes through a batch of 32 rays.
+//  * The instances are taken one after the other by the whole warp: a vote skips an instance no lane's ray reaches, the
+//    lanes meet again after every instance, and the order is nearest first for the warp as a whole (mean distance at
+//    which its rays enter the instance's world box), so the hit found in the nearer instance culls the farther one's box.
+//    trace_scene's per-lane loop lets lanes drift into different instances, which then run the same traversal code one
+//    after the other, and visits the instances in index order: C3 8.48 -> 8.31 ms by the stepping, -> 7.74 ms by the
+//    order (798 M instead of 884 M node visits per frame); profiles/r02_migrate.txt.
+//  * CUT = true (RT_MIGRATE = T > 0, opt-in, measured slower): a batch ends when no more than T of the lanes traversing
+//    an instance are left; those lanes write their traversal state (node, stack, closest hit so far, instance) to a
+//    buffer private to the warp and the warp takes the next batch; when the buffer holds a batch's worth (or the queue
+//    is empty) the warp resumes those rays together, from where they stopped - long rays share warps with long rays.
+//    The check (one LDS, one compare, one more loop exit) costs the loop 20-25 % however rarely it fires.
+// Binary layout, instances looped (no top-level tree), one-warp CTAs.
 constexpr int MIG_STACK = 40;   // deepest stack a ray may have when it is set aside (deeper ones keep running)
 struct __align__(16) MigEntry {
   uint32_t idx, where, node;     // ray, (instance | stack depth << 8), node to visit next
@@ -805,7 +811,7 @@ __device__ __forceinline__ bool trace_bvh2_mig(const BlasDev& b, const RayObj& r
 
 template <bool COUNT, bool CUT>
 __global__ void __launch_bounds__(32, 32)
-    k_trace_shade_mig(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt0, uint32_t bounce, const float4* __restrict__ rayO,
+    k_trace_shade_step(SceneDev scene, FrameUniforms U, uint32_t* __restrict__ cnt0, uint32_t bounce, const float4* __restrict__ rayO,
                       const float4* __restrict__ rayD, float4* __restrict__ nextO, float4* __restrict__ nextD,
                       float4* __restrict__ shadowQ, float4* __restrict__ sample, rt_hit* __restrict__ primary,
                       unsigned long long* __restrict__ stats64, MigEntry* __restrict__ mig, int T, int F) {
@@ -1305,7 +1311,7 @@ struct FramePipeline {
     size_t alive_cap = 0;
     cudaEvent_t done = nullptr;
   } sub[RT_MAX_SUB];
-  MigEntry* mig = nullptr;       // k_trace_shade_mig: 32 entries per resident warp and sub-frame
+  MigEntry* mig = nullptr;       // k_trace_shade_step: 32 entries per resident warp and sub-frame
   size_t mig_blocks = 0;
   // early resolve of the tiles k_raygen finished
   uint32_t* tile_live = nullptr;
@@ -1516,11 +1522,11 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   static const bool fuse_shade_env = getenv("RT_FUSE_SHADE") ? atoi(getenv("RT_FUSE_SHADE")) != 0 : true;
   const bool fuse_shade = fuse_shade_env && !may_sort && !(accel == ACCEL_WIDE && wave_on && rq.scene.tlas == nullptr);
   // RT_MIGRATE = T: a batch of the closest-hit launch ends when no more than T of its rays are still traversing; the
-  // stragglers are set aside with their traversal state and resumed together (k_trace_shade_mig)
+  // stragglers are set aside with their traversal state and resumed together (k_trace_shade_step)
   static const int migrate_F = getenv("RT_MIGRATE_FLUSH") ? std::max(1, atoi(getenv("RT_MIGRATE_FLUSH"))) : 32;   // resume when this many are set aside
   static const int migrate_env = getenv("RT_MIGRATE") ? std::max(0, std::min(16, atoi(getenv("RT_MIGRATE")))) : 0;
   // Binary layout, instances looped: the closest-hit launch takes the instances one after the other with the whole warp in
-  // step (k_trace_shade_mig<., false>: an instance no lane reaches is skipped by one vote, the lanes meet again after
+  // step (k_trace_shade_step<., false>: an instance no lane reaches is skipped by one vote, the lanes meet again after
   // each instance): C3 8.48 -> 8.31 ms, a 1/8 shard of C4 4.38 -> 4.28.  RT_INSTANCE_STEP=0: the generic k_trace_shade.
   static const bool step_env = getenv("RT_INSTANCE_STEP") ? atoi(getenv("RT_INSTANCE_STEP")) != 0 : true;
   const bool steppable = fuse_shade && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && rq.scene.n_inst <= 4u && RT_TRACE_THREADS == 32;
@@ -1537,7 +1543,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   const bool migrate = migrate_env > 0 && steppable;
   const int migrate_T = migrate ? std::min(migrate_env, 16 / (int)std::max(1u, rq.scene.n_inst)) : 0;   // the buffer holds 32
   if (migrate && !p->mig) {
-    p->mig_blocks = (size_t)std::min(persistent_blocks(k_trace_shade_mig<false, true>, 32), persistent_blocks(k_trace_shade_mig<true, true>, 32));
+    p->mig_blocks = (size_t)std::min(persistent_blocks(k_trace_shade_step<false, true>, 32), persistent_blocks(k_trace_shade_step<true, true>, 32));
     RT_CUDA_TRY(cudaMalloc(&p->mig, (size_t)RT_MAX_SUB * p->mig_blocks * 32 * sizeof(MigEntry)), err);
   }
   const bool fused = fused_env && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && !may_sort && rq.scene.n_inst <= 32u;
@@ -1714,7 +1720,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   }
     RT_CUDA_TRY(cudaEventRecord(sb.kev[4 * j + 0], cs), err);
 #define CALL_STEPPED(C, CUT, BLOCKS, MG, T)                                                                                   \
-  k_trace_shade_mig<C, CUT><<<BLOCKS, 32, 0, cs>>>(rq.scene, U, c.cnt, j, c.rayO[cur], c.rayD[cur], c.rayO[cur ^ 1], c.rayD[cur ^ 1], \
+  k_trace_shade_step<C, CUT><<<BLOCKS, 32, 0, cs>>>(rq.scene, U, c.cnt, j, c.rayO[cur], c.rayD[cur], c.rayO[cur ^ 1], c.rayD[cur ^ 1], \
                                                    c.shadowQ, p->sample, prim, p->stats64, MG, T, migrate_F)
     if (migrate) {
       MigEntry* mg = p->mig + (size_t)(&c - ctx) * p->mig_blocks * 32;
@@ -1722,7 +1728,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
       else CALL_STEPPED(false, true, (int)p->mig_blocks, mg, migrate_T);
     } else if (stepped) {
       static int sb_blocks[2] = {0, 0};
-      if (!sb_blocks[0]) { sb_blocks[0] = persistent_blocks(k_trace_shade_mig<false, false>, 32); sb_blocks[1] = persistent_blocks(k_trace_shade_mig<true, false>, 32); }
+      if (!sb_blocks[0]) { sb_blocks[0] = persistent_blocks(k_trace_shade_step<false, false>, 32); sb_blocks[1] = persistent_blocks(k_trace_shade_step<true, false>, 32); }
       if (counting) CALL_STEPPED(true, false, sb_blocks[1], nullptr, 0);
       else CALL_STEPPED(false, false, sb_blocks[0], nullptr, 0);
     } else

@@ -29,6 +29,8 @@ import time
 
 import numpy as np
 
+# kernels are loaded when the library is, not at their first launch: `build_ms` times the build, not the driver's lazy loader
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))

@@ -209,15 +209,35 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev scene, FrameUniforms U,
   const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const f3 amb = ambient_color();
   uint32_t culled = 0;
+  // slot -> (pixel, sample) is seven integer divisions per slot in the general case (slot_to_pixel); with samples per pixel
+  // and tile sides that are powers of two (the defaults: 4, 64 x 64) six of them are shifts and masks.  ncu: this kernel is
+  // issue-bound (76 % of the slots busy) and a fifth of its instructions were those divisions.
+  const uint32_t tile_px = U.tile_w * U.tile_h;
+  const bool p2 = (U.spp & (U.spp - 1)) == 0 && (tile_px & (tile_px - 1)) == 0 && (U.tile_w & (U.tile_w - 1)) == 0 && U.tile_w >= 8;
+  const int sh_spp = __ffs((int)U.spp) - 1, sh_tpx = __ffs((int)tile_px) - 1, sh_bx = __ffs((int)(U.tile_w >> 3)) - 1;
   for (uint64_t base = (uint64_t)w * 32; base < nslots; base += (uint64_t)warps * 32) {
     const uint32_t s = slot_base + (uint32_t)base + lane_id();
     bool valid = false, reach = false;
     f3 o = mk3(0, 0, 0), d = mk3(0, 0, 0);
+    uint32_t smp = 0;
     if ((uint32_t)base + lane_id() < nslots) {
       uint32_t x, y;
-      valid = slot_to_pixel(U, s / U.spp, x, y);
+      if (p2) {
+        const uint32_t pix = s >> sh_spp, lt = pix >> sh_tpx, in = pix & (tile_px - 1u);
+        smp = s & (U.spp - 1u);
+        const uint32_t tile = lt * U.shard_count + U.shard_index;
+        const uint32_t blk = in >> 5, l = in & 31u;
+        const uint32_t tx = ((blk & ((U.tile_w >> 3) - 1u)) << 3) + (l & 7u), ty = ((blk >> sh_bx) << 2) + (l >> 3);
+        const uint32_t trow = tile / U.tiles_x;
+        x = (tile - trow * U.tiles_x) * U.tile_w + tx;
+        y = trow * U.tile_h + ty;
+        valid = x < U.width && y < U.height;
+      } else {
+        valid = slot_to_pixel(U, s / U.spp, x, y);
+        smp = s % U.spp;
+      }
       if (valid) {
-        raygen(U, x, y, s % U.spp, o, d);
+        raygen(U, x, y, smp, o, d);
         RayObj rw;
         rw.o = o;
         rw.idir = mk3(safe_rcp_dir(d.x), safe_rcp_dir(d.y), safe_rcp_dir(d.z));
@@ -239,7 +259,7 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev scene, FrameUniforms U,
           if (primary) {
             rt_hit out;
             out.instance = RT_MISS; out.primitive = RT_MISS; out.t = 0.0f; out.u = 0.0f; out.v = 0.0f;
-            primary[((size_t)y * U.width + x) * U.spp + (s % U.spp)] = out;
+            primary[((size_t)y * U.width + x) * U.spp + smp] = out;
           }
         }
       } else {
@@ -249,7 +269,7 @@ __global__ void __launch_bounds__(256) k_raygen(SceneDev scene, FrameUniforms U,
     // a tile none of whose rays reaches the scene is final here: k_resolve stores it while the rest is traced
     // (a warp's 32 slots lie in one tile)
     if (tile_live && __any_sync(0xFFFFFFFFu, reach) && lane_id() == 0)
-      tile_live[(slot_base + (uint32_t)base) / (U.tile_w * U.tile_h * U.spp)] = 1u;
+      tile_live[p2 ? (slot_base + (uint32_t)base) >> (sh_tpx + sh_spp) : (slot_base + (uint32_t)base) / (tile_px * U.spp)] = 1u;
     const uint32_t dst = warp_append(reach, &cnt[C_NRAY]);
     if (reach) {
       rayO[dst] = make_float4(o.x, o.y, o.z, __uint_as_float(s));

@@ -1525,7 +1525,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
   // puts everything back on one stream.
   static const bool shadow_async = getenv("RT_SHADOW_STREAM") ? atoi(getenv("RT_SHADOW_STREAM")) != 0 : true;
   static const int sub_env = getenv("RT_SUBFRAMES") ? atoi(getenv("RT_SUBFRAMES")) : 2;
-  static const uint64_t sub_min_slots = getenv("RT_SUBFRAMES_MIN") ? strtoull(getenv("RT_SUBFRAMES_MIN"), nullptr, 10) : (12ull << 20);
+  static const uint64_t sub_min_slots = getenv("RT_SUBFRAMES_MIN") ? strtoull(getenv("RT_SUBFRAMES_MIN"), nullptr, 10) : (6ull << 20);
   const bool may_sort = accel != ACCEL_BRUTE && sort_from <= (int)U.max_bounce && sort_from <= sort_to;
   const bool wave = accel == ACCEL_WIDE && wave_on && rq.scene.tlas == nullptr;
   // The bounce-fused path kernel (rt_path.cuh): binary BVH, instances looped (no top-level tree).

@@ -704,6 +704,8 @@ print('PARITY OK', sc.stats()['kernel_launches'])
     {"RT_MIGRATE": "12", "RT_SUBFRAMES": "1"},
     {"RT_MIGRATE": "1", "RT_SUBFRAMES": "3", "RT_SUBFRAMES_MIN": "1"},
     {"RT_TLAS_STEP": "0", "RT_SHADOW_TLAS_STEP": "0"},   # top-level tree walked per lane (trace_scene) instead of with the warp in step
+    {"RT_TAIL_FROM": "0"},                               # deep bounce limits bounce by bounce instead of the path-kernel tail
+    {"RT_TAIL_FROM": "3"},
     {"RT_SHADOW_STEP": "1"},                             # shadow rays through looped instances with the warp in step
     {"RT_INSTANCE_STEP": "0"},                           # the generic closest-hit + shading launch (trace_scene) for looped instances
     {"RT_FUSE_SHADE": "0"},                              # separate shading kernels between the traversal launches (round 1)

@@ -1567,6 +1567,12 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     RT_CUDA_TRY(cudaMalloc(&p->mig, (size_t)RT_MAX_SUB * p->mig_blocks * 32 * sizeof(MigEntry)), err);
   }
   const bool fused = fused_env && accel == ACCEL_BVH2 && rq.scene.tlas == nullptr && !may_sort && rq.scene.n_inst <= 32u;
+  // Deep bounce limits (the reference's default MAX_BOUNCE_COUNT is 63): from bounce RT_TAIL_FROM (9) on, the rest of every
+  // path runs in ONE launch of the path kernel per sub-frame instead of two launches and a host look per bounce - by then
+  // a few thousand rays are left, and what a bounce costs is its launches and the round trip of its ray count.
+  static const uint32_t tail_from = getenv("RT_TAIL_FROM") ? (uint32_t)atoi(getenv("RT_TAIL_FROM")) : 9u;
+  const bool tail = !fused && fuse_shade && tail_from > 0u && U.max_bounce >= tail_from && accel == ACCEL_BVH2 &&
+                    rq.scene.tlas == nullptr && rq.scene.n_inst <= 32u;
   const int nsub = (sub_env >= 2 && nslots >= sub_min_slots && !may_sort && !wave)
                        ? (int)std::min<uint32_t>((uint32_t)std::min(sub_env, RT_MAX_SUB), U.n_local_tiles) : 1;
 
@@ -1771,7 +1777,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
       c.cur ^= 1;
       RT_CUDA_TRY(cudaMemcpyAsync(&sb.h_alive[j + 1], cn + C_NRAY, sizeof(uint32_t), cudaMemcpyDeviceToHost, cs), err);
       RT_CUDA_TRY(cudaEventRecord(sb.aev[j + 1], cs), err);
-      if (j + 1 > 8) { RT_CUDA_TRY(cudaEventSynchronize(sb.aev[j + 1]), err); }
+      if (j + 1 > 8 && !tail) { RT_CUDA_TRY(cudaEventSynchronize(sb.aev[j + 1]), err); }
       for (uint32_t k = 1; k <= j + 1 && !c.dead; k++)
         c.dead = cudaEventQuery(sb.aev[k]) == cudaSuccess && sb.h_alive[k] == 0u;
     }
@@ -1826,7 +1832,7 @@ int pipeline_render(FramePipeline* p, const FrameRequest& rq, cudaStream_t st, r
     }
   } else
   for (uint32_t j = 0; j <= U.max_bounce; j++) {
-    if (fused && j >= fuse_from) {
+    if ((fused && j >= fuse_from) || (tail && j >= tail_from)) {
       for (int k = 0; k < nsub; k++) {
         if (ctx[k].dead) continue;
         rc = enqueue_path(ctx[k], j);

@@ -381,4 +381,23 @@ int emu_slot_to_pixel(const rt_frame_params* p, uint32_t pslot, uint32_t* x, uin
   return slot_to_pixel(U, pslot, *x, *y) ? 1 : 0;
 }
 
+// the three node tests of rt_trav.cuh on explicit (ray, box) pairs: bit 0 = slab_interval (subtract, multiply, two-sided
+// margins), bit 1 = slab_interval_fma (the default: one fma per plane), bit 2 = slab_interval_sel (near / far picked by sign)
+int emu_slab_tests(uint64_t n, const float* o, const float* d, const float* box, float tmin, const float* tmax, uint8_t* out) {
+  for (uint64_t i = 0; i < n; i++) {
+    const RayObj r = ray_setup(mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]));
+    const float* b = box + 6 * i;
+    float tn, tf;
+    uint8_t m = 0;
+    slab_interval(r, b[0], b[1], b[2], b[3], b[4], b[5], tmin, tmax[i], tn, tf);
+    if (tn <= tf) m |= 1;
+    slab_interval_fma(r, b[0], b[1], b[2], b[3], b[4], b[5], tmin, tmax[i], tn, tf);
+    if (tn <= tf) m |= 2;
+    slab_interval_sel(r, b[0], b[1], b[2], b[3], b[4], b[5], tmin, tmax[i], tn, tf);
+    if (tn <= tf) m |= 4;
+    out[i] = m;
+  }
+  return 0;
+}
+
 }  // extern "C"

@@ -97,6 +97,19 @@ def slot_to_pixel(params, pslot):
     return bool(ok), x.value, y.value
 
 
+def slab_tests(o, d, box, tmin, tmax):
+    """The node tests of rt_trav.cuh on explicit (ray, box) pairs: uint8 per pair, bit 0 = round-1 test, bit 1 = the
+    default one-fma test, bit 2 = the sign-select variant."""
+    o = np.ascontiguousarray(o, np.float32); d = np.ascontiguousarray(d, np.float32)
+    box = np.ascontiguousarray(box, np.float32); tmax = np.ascontiguousarray(tmax, np.float32)
+    n = o.shape[0]
+    out = np.zeros(n, np.uint8)
+    f = lib().emu_slab_tests
+    f.argtypes = [C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p]
+    assert f(n, o.ctypes.data, d.ctypes.data, box.ctypes.data, float(tmin), tmax.ctypes.data, out.ctypes.data) == 0
+    return out
+
+
 def treelet(boxes, leaf_cost):
     """Device treelet optimisation of one root over n <= 7 leaves (emu_treelet): returns
     (cost of the initial chain, cost after, left[n-1], right[n-1])."""

@@ -306,3 +306,50 @@ def test_slot_to_pixel_is_a_bijection(rt, emu, w, h, tw, th, n):
                 seen[y, x] += 1
                 assert ((y // th) * ((w + tw - 1) // tw) + x // tw) % n == s
     assert (seen == 1).all()
+
+
+def test_node_tests_are_conservative(emu):
+    """The box test only has to be conservative: a ray that reaches a point of a mesh must pass the
+    test of every padded box around that point when the far limit is exactly the distance of the point (best.t == t of
+    the hit, the tightest the traversal ever makes it).  Checked for the round-1 test and the two round-2 tests (one fma
+    per plane: the default; near / far planes picked by sign) against float64 geometry: origins from inside the mesh out
+    to 10 000 mesh extents, axis-parallel and near-parallel directions, flat and point-sized boxes, points on box faces."""
+    rng = np.random.default_rng(5)
+    n = 400000
+    M = 10.0 ** rng.uniform(-2, 3, n)                                   # max |coordinate| of the mesh the box belongs to
+    c = rng.uniform(-1, 1, (n, 3)) * M[:, None] * 0.9                  # box centre inside the mesh bounds
+    half = 10.0 ** rng.uniform(-6, -0.5, (n, 3)) * M[:, None]
+    half[rng.random((n, 3)) < 0.15] = 0.0                              # flat / degenerate boxes
+    lo, hi = c - half, c + half
+    p = lo + rng.random((n, 3)) * (hi - lo)                            # the point the ray reaches ...
+    face = rng.random(n) < 0.3                                         # ... sometimes exactly on a face of the box
+    ax = rng.integers(0, 3, n)
+    p[face, ax[face]] = np.where(rng.random(face.sum()) < 0.5, lo[face, ax[face]], hi[face, ax[face]])
+    d = rng.normal(0, 1, (n, 3))
+    par = rng.random(n) < 0.3                                          # axis-parallel and nearly parallel directions
+    k = rng.integers(0, 3, n)
+    for a in range(3):
+        sel = par & (k != a)
+        d[sel, a] *= 10.0 ** rng.uniform(-30, -3, sel.sum())
+    d[rng.random(n) < 0.05, rng.integers(0, 3)] = 0.0
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    dist = 10.0 ** rng.uniform(-3, 4, n) * M                           # origin 0.001 ... 10 000 mesh extents away
+    o64 = p - d * dist[:, None]
+    # what the kernels see: float32 box (leaf padding of rt_build.cu: 4e-6 * max |coordinate|, rounded outward), float32 ray
+    pad = (M * 4e-6 + 1e-30)[:, None]
+    lo32 = np.nextafter((lo - pad).astype(np.float32), np.float32(-np.inf))
+    hi32 = np.nextafter((hi + pad).astype(np.float32), np.float32(np.inf))
+    o32, d32 = o64.astype(np.float32), d.astype(np.float32)
+    ok = (np.linalg.norm(d32, axis=1) > 0.5)
+    # distance of the point along the float32 ray, as the triangle test would report it (float64, rounded up one ulp)
+    dd = d32.astype(np.float64)
+    t = ((p - o32.astype(np.float64)) * dd).sum(1) / (dd * dd).sum(1)
+    # the float32 ray does not pass exactly through p any more: keep the pairs whose ray still comes within the padding
+    closest = o32.astype(np.float64) + dd * t[:, None]
+    ok &= (np.abs(closest - p) <= 0.25 * pad).all(1) & (t > 0.002) & (t < 9000.0)
+    tmax = np.nextafter(t.astype(np.float32), np.float32(np.inf))
+    m = emu.slab_tests(o32[ok], d32[ok], np.concatenate([lo32, hi32], 1)[ok], 0.001, tmax[ok])
+    assert ok.sum() > 100000
+    for bit, name in ((1, "slab_interval"), (2, "slab_interval_fma"), (4, "slab_interval_sel")):
+        missed = np.flatnonzero((m & bit) == 0)
+        assert missed.size == 0, (name, missed.size, missed[:5])

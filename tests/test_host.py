@@ -237,3 +237,16 @@ def test_host_normals_equal_a_numpy_restatement(rt):
     assert np.array_equal(got[:, 3:], ref)
     assert np.array_equal(got[:, :3], v[:, :3])
     assert np.array_equal(got[-1, 3:], [0, 1, 0])
+
+
+def test_committed_ncu_capture_belongs_to_the_committed_kernels():
+    """profiles/traffic.json (DRAM bytes, warp / thread instructions of one C3 frame's traversal launches, from ncu) carries
+    the hash of the CUDA sources it was captured from; bench.py prints roofline.traffic / issue_frac / simd_lanes only when
+    that hash is the hash of the sources it runs.  A change of a kernel without a new capture shows up here."""
+    import json
+    import sys
+    sys.path.insert(0, ROOT)
+    import bench
+    t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    assert t["source_hash"] == bench.source_hash()
+    assert t["launches"] == 36 and t["k_trace_dram_bytes_per_frame"] > 0
